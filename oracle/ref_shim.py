@@ -1,0 +1,47 @@
+"""Import the UNMODIFIED reference quantizer from /root/reference (authoring container only).
+
+TEST INFRASTRUCTURE ONLY.  /root/reference does not exist on the GPU box, so nothing that runs
+there (`-m gpu` tests, smoke(), bench.py) may call this; it is used by tests/golden/make_golden.py
+and by CPU tests that skip when the reference is absent.
+
+Two obstacles, neither needs a change to the reference:
+  * `audiocraft/__init__.py` imports data/models/modules, which need packages that are not
+    installed -> register an empty `audiocraft` package whose __path__ points at the reference so
+    that `audiocraft.quantization` imports without running that __init__.
+  * `core_vq.py:10` imports `flashy` (not installed) -> a stub whose distrib.broadcast_tensors /
+    average_tensors do nothing (single process: nothing to synchronise).
+"""
+from __future__ import annotations
+
+import os
+import sys
+import types
+
+REFERENCE_ROOT = os.environ.get("RVQ_REFERENCE_ROOT", "/root/reference")
+
+
+def available() -> bool:
+    return os.path.isfile(os.path.join(REFERENCE_ROOT, "audiocraft", "quantization", "core_vq.py"))
+
+
+def load():
+    """Returns the reference's `audiocraft.quantization` module."""
+    if not available():
+        raise RuntimeError(f"reference not found under {REFERENCE_ROOT}")
+    if "flashy" not in sys.modules:
+        flashy = types.ModuleType("flashy")
+        distrib = types.ModuleType("flashy.distrib")
+        distrib.broadcast_tensors = lambda tensors, src=0: None
+        distrib.average_tensors = lambda tensors: None
+        distrib.is_distributed = lambda: False
+        distrib.world_size = lambda: 1
+        distrib.rank = lambda: 0
+        flashy.distrib = distrib
+        sys.modules["flashy"] = flashy
+        sys.modules["flashy.distrib"] = distrib
+    if "audiocraft" not in sys.modules or not hasattr(sys.modules["audiocraft"], "__path__"):
+        pkg = types.ModuleType("audiocraft")
+        pkg.__path__ = [os.path.join(REFERENCE_ROOT, "audiocraft")]
+        sys.modules["audiocraft"] = pkg
+    import importlib
+    return importlib.import_module("audiocraft.quantization")

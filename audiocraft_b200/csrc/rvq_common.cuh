@@ -1,0 +1,116 @@
+// rvq_common.cuh -- shared definitions of librvq_b200.so (sm_100a only).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <cuda_fp16.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "../../include/rvq_b200.h"
+
+#if defined(__CUDA_ARCH__) && (__CUDA_ARCH__ < 1000)
+#error "librvq_b200 is written for sm_100a (B200) only"
+#endif
+
+#define RVQ_PACK_MAGIC 0x52565142u /* "RVQB" */
+
+// Per-stage metadata written by rvq_pack_codebooks.
+struct RvqStageMeta {
+    float cmax_abs;     // max |E[c][d]| over the codebook (finite part)
+    float cnorm2_max;   // max ||E_c||^2 (canonical order)
+    int32_t scale_exp;  // fp16 operand copy = E * 2^scale_exp
+    int32_t nonfinite;  // != 0: the codebook holds NaN/Inf -> tensor-core search is not used
+};
+
+// First 256 bytes of a pack, followed by the sections at the byte offsets below.
+struct RvqPackHeader {
+    uint32_t magic;
+    int32_t Ktot, C, D;
+    int64_t off_meta;   // RvqStageMeta[Ktot]
+    int64_t off_embed;  // float [Ktot][C][D]
+    int64_t off_cnorm;  // float [Ktot][C]
+    int64_t off_f16;    // __half [Ktot][C][D] (scaled by 2^scale_exp), 0 if absent
+    int64_t total_bytes;
+};
+
+static inline __host__ __device__ int64_t rvq_align_up(int64_t v, int64_t a) { return (v + a - 1) / a * a; }
+
+static inline __host__ RvqPackHeader rvq_pack_layout(int Ktot, int C, int D) {
+    RvqPackHeader h;
+    h.magic = RVQ_PACK_MAGIC;
+    h.Ktot = Ktot; h.C = C; h.D = D;
+    int64_t off = 256;
+    h.off_meta = off;  off = rvq_align_up(off + (int64_t)sizeof(RvqStageMeta) * Ktot, 256);
+    h.off_embed = off; off = rvq_align_up(off + (int64_t)4 * Ktot * C * D, 256);
+    h.off_cnorm = off; off = rvq_align_up(off + (int64_t)4 * Ktot * C, 256);
+    h.off_f16 = off;   off = rvq_align_up(off + (int64_t)2 * Ktot * C * D, 1024);
+    h.total_bytes = off;
+    return h;
+}
+
+// Views into a pack (device pointers; computed on the host from the layout).
+struct RvqPackView {
+    const RvqStageMeta *meta;
+    const float *embed;
+    const float *cnorm;
+    const __half *f16;
+    int Ktot, C, D;
+};
+
+static inline __host__ RvqPackView rvq_pack_view(const void *pack, int Ktot, int C, int D) {
+    RvqPackHeader h = rvq_pack_layout(Ktot, C, D);
+    const char *p = (const char *)pack;
+    RvqPackView v;
+    v.meta = (const RvqStageMeta *)(p + h.off_meta);
+    v.embed = (const float *)(p + h.off_embed);
+    v.cnorm = (const float *)(p + h.off_cnorm);
+    v.f16 = (const __half *)(p + h.off_f16);
+    v.Ktot = Ktot; v.C = C; v.D = D;
+    return v;
+}
+
+// ---- error plumbing (host) ----
+void rvq_set_error(const char *fmt, ...);
+void rvq_count_launch(int n);
+int rvq_check_launch(const char *what);  // cudaGetLastError -> RVQ_ECUDA
+
+#define RVQ_REQUIRE(cond, code, ...)            \
+    do {                                        \
+        if (!(cond)) {                          \
+            rvq_set_error(__VA_ARGS__);         \
+            return (code);                      \
+        }                                       \
+    } while (0)
+
+#define RVQ_CUDA(call)                                                                   \
+    do {                                                                                 \
+        cudaError_t e_ = (call);                                                         \
+        if (e_ != cudaSuccess) {                                                         \
+            rvq_set_error("%s failed: %s", #call, cudaGetErrorString(e_));               \
+            return RVQ_ECUDA;                                                            \
+        }                                                                                \
+    } while (0)
+
+// ---- canonical arithmetic (device) ----
+// Canonical inner product (defined in DESIGN.md, "canonical order"): lane l of a warp owns elements
+// 128*chunk + 4*l + {0,1,2,3}; partials advance with one fused multiply-add per element in
+// increasing d; lanes are combined with the xor butterfly 16, 8, 4, 2, 1.  Every lane ends up with
+// the same bits (fp32 add is commutative), so any lane's copy is "the" result.
+__device__ __forceinline__ float rvq_butterfly(float p) {
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) p = __fadd_rn(p, __shfl_xor_sync(0xffffffffu, p, off));
+    return p;
+}
+
+// torch.max semantics (core_vq.py:171): NaN beats everything, first index wins ties.
+__device__ __forceinline__ bool rvq_better(float s, int i, float best, int bi) {
+    bool sn = s != s, bn = best != best;
+    if (sn || bn) return (sn && !bn) || (sn && bn && i < bi);
+    return (s > best) || (s == best && i < bi);
+}
+
+// score of a code: -((xx - 2*dot) + cc), one rounding per operation (core_vq.py:166-170)
+__device__ __forceinline__ float rvq_score(float xx, float dot, float cc) {
+    float two_dot = __fmul_rn(2.0f, dot);
+    return -__fadd_rn(__fsub_rn(xx, two_dot), cc);
+}

@@ -1,0 +1,160 @@
+// rvq_decode.cu -- ResidualVectorQuantization.decode (core_vq.py:399-405) as one gather-sum kernel.
+//
+//   out[b, :, t] = 0.0f + E_0[codes[b,0,t]] + E_1[codes[b,1,t]] + ...      (stage order, fp32)
+//
+// HBM-bound: per frame 8*K bytes of codes in and 4*D bytes out; the codebooks (K*C*D*4 bytes,
+// 4 MB for MusicGen) stay L2 resident.  One warp owns 32 consecutive frames: it reads their codes
+// coalesced (lane = frame), then walks the frames with lane = 4 consecutive dims so that every
+// codebook row is one coalesced 128-bit-per-lane read and every output row one coalesced
+// 128-bit-per-lane streaming store.  The K row reads of a frame are issued before the first add.
+#include "rvq_common.cuh"
+
+template <typename CodeT>
+__device__ __forceinline__ long long load_code(const void *codes, int64_t idx) {
+    return (long long)reinterpret_cast<const CodeT *>(codes)[idx];
+}
+
+// DCH = D / 128 when D is 128/256/512 (unrolled), else 0 -> generic chunk loop.
+// Dynamic shared memory: int32 codes [warps][K][32] of the 32 frames a warp is working on
+// (-1 = out of range, skipped).
+template <typename CodeT, int DCH>
+__global__ void __launch_bounds__(256)
+rvq_decode_kernel(const void *__restrict__ codes, int64_t cs_b, int64_t cs_k, int64_t cs_t, int B, int K, int T,
+                  const float *__restrict__ embed, int C, int D, float *__restrict__ out, int64_t os_b,
+                  int64_t os_d, int64_t os_t, int64_t *__restrict__ status) {
+    extern __shared__ int s_codes[];
+    const int lane = threadIdx.x & 31;
+    const int wib = threadIdx.x >> 5;
+    const int warps_per_block = blockDim.x >> 5;
+    int *wcodes = s_codes + (size_t)wib * K * 32;
+    const int64_t tblocks = (T + 31) / 32;  // 32-frame groups per batch item
+    const int64_t ngroups = (int64_t)B * tblocks;
+    const int nchunks = DCH > 0 ? DCH : (D + 127) / 128;
+
+    for (int64_t g = (int64_t)blockIdx.x * warps_per_block + wib; g < ngroups;
+         g += (int64_t)gridDim.x * warps_per_block) {
+        const int64_t b = g / tblocks;
+        const int t0 = (int)(g % tblocks) * 32;
+        const int nf = min(32, T - t0);
+        __syncwarp();
+        // lane = frame: coalesced read of the K codes of this lane's frame
+        for (int k = 0; k < K; ++k) {
+            int v = -1;
+            if (lane < nf) {
+                long long c = load_code<CodeT>(codes, b * cs_b + k * cs_k + (int64_t)(t0 + lane) * cs_t);
+                if (c < 0 || c >= C) {
+                    unsigned long long flat = 1ull + (unsigned long long)((b * K + k) * (long long)T + t0 + lane);
+                    atomicExch((unsigned long long *)&status[0], 1ull);
+                    // keep the smallest flat index; 0 means "none yet"
+                    unsigned long long *s1 = (unsigned long long *)&status[1];
+                    unsigned long long old = *s1;
+                    while (old == 0ull || flat < old) {
+                        unsigned long long prev = atomicCAS(s1, old, flat);
+                        if (prev == old) break;
+                        old = prev;
+                    }
+                } else {
+                    v = (int)c;
+                }
+            }
+            wcodes[k * 32 + lane] = v;
+        }
+        __syncwarp();
+        // lane = 4 consecutive dims: walk the frames
+        for (int f = 0; f < nf; ++f) {
+            for (int ch = 0; ch < nchunks; ++ch) {
+                const int d = ch * 128 + lane * 4;
+                if (DCH == 0 && d >= D) break;
+                float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);  // quantized_out = 0.0 (core_vq.py:400)
+                for (int k0 = 0; k0 < K; k0 += 8) {
+                    float4 row[8];
+                    int code[8];
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        code[j] = (k0 + j < K) ? wcodes[(k0 + j) * 32 + f] : -1;
+                        row[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+                        if (code[j] >= 0)
+                            row[j] = __ldg(reinterpret_cast<const float4 *>(
+                                embed + ((int64_t)(k0 + j) * C + code[j]) * D + d));
+                    }
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        if (code[j] >= 0) {  // stage order (core_vq.py:401-404)
+                            acc.x = __fadd_rn(acc.x, row[j].x);
+                            acc.y = __fadd_rn(acc.y, row[j].y);
+                            acc.z = __fadd_rn(acc.z, row[j].z);
+                            acc.w = __fadd_rn(acc.w, row[j].w);
+                        }
+                    }
+                }
+                float *o = out + b * os_b + (int64_t)(t0 + f) * os_t + (int64_t)d * os_d;
+                if (os_d == 1) {
+                    __stcs(reinterpret_cast<float4 *>(o), acc);  // streaming: keep the codebooks in L2
+                } else {
+                    o[0] = acc.x; o[os_d] = acc.y; o[2 * os_d] = acc.z; o[3 * os_d] = acc.w;
+                }
+            }
+        }
+    }
+}
+
+template <typename CodeT>
+static int launch_decode(const void *codes, const int64_t cs[3], int B, int K, int T, const RvqPackView &pv,
+                         float *out, const int64_t os[3], int64_t *status, cudaStream_t stream) {
+    const int64_t ngroups = (int64_t)B * ((T + 31) / 32);
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const int wpb = K <= 32 ? 8 : 4;
+    const size_t smem = (size_t)wpb * K * 32 * sizeof(int);
+    int64_t blocks = (ngroups + wpb - 1) / wpb;
+    const int64_t cap = (int64_t)sms * 8 * 4;  // grid-stride beyond a few waves of resident CTAs
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+#define RVQ_DEC_LAUNCH(DCH)                                                                              \
+    rvq_decode_kernel<CodeT, DCH><<<(unsigned)blocks, wpb * 32, smem, stream>>>(                         \
+        codes, cs[0], cs[1], cs[2], B, K, T, pv.embed, pv.C, pv.D, out, os[0], os[1], os[2], status)
+    if (pv.D == 128) RVQ_DEC_LAUNCH(1);
+    else if (pv.D == 256) RVQ_DEC_LAUNCH(2);
+    else if (pv.D == 512) RVQ_DEC_LAUNCH(4);
+    else RVQ_DEC_LAUNCH(0);
+#undef RVQ_DEC_LAUNCH
+    rvq_count_launch(1);
+    return rvq_check_launch("rvq_decode_kernel");
+}
+
+// K == 0: the reference returns the scalar 0.0; the wrapper never calls with K == 0 on a
+// non-empty output, but keep the ABI total: fill with +0.0f.
+__global__ void rvq_fill_zero_kernel(float *__restrict__ out, int64_t os_b, int64_t os_d, int64_t os_t, int B,
+                                     int D, int T) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    int64_t total = (int64_t)B * D * T;
+    if (i >= total) return;
+    int64_t d = i % D, t = (i / D) % T, b = i / ((int64_t)D * T);
+    out[b * os_b + d * os_d + t * os_t] = 0.0f;
+}
+
+extern "C" int rvq_decode_f32(const void *codes, int code_bytes, const int64_t cs[3], int B, int K, int T,
+                              const void *pack, int Ktot, int C, int D, float *out, const int64_t os[3],
+                              int64_t *status, void *stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    RVQ_REQUIRE(B >= 0 && K >= 0 && T >= 0, RVQ_EINVAL, "rvq_decode_f32: negative size");
+    if ((int64_t)B * T == 0) return RVQ_OK;
+    RVQ_REQUIRE(pack && out && os && status, RVQ_EINVAL, "rvq_decode_f32: null pointer");
+    RVQ_REQUIRE(Ktot > 0 && Ktot <= RVQ_MAX_STAGES && C > 0 && D > 0, RVQ_EINVAL, "rvq_decode_f32: bad pack sizes");
+    RVQ_REQUIRE(K <= Ktot, RVQ_EINVAL, "rvq_decode_f32: %d code streams but only %d codebooks", K, Ktot);
+    RVQ_REQUIRE(D % 4 == 0, RVQ_EUNSUPPORTED, "rvq_decode_f32: dimension %d is not a multiple of 4", D);
+    RVQ_REQUIRE(os[1] != 1 || (((uintptr_t)out & 15) == 0 && os[0] % 4 == 0 && os[2] % 4 == 0), RVQ_EINVAL,
+                "rvq_decode_f32: out must be 16-byte aligned with strides that are multiples of 4");
+    RvqPackView pv = rvq_pack_view(pack, Ktot, C, D);
+    if (K == 0) {
+        int64_t total = (int64_t)B * D * T;
+        rvq_fill_zero_kernel<<<(unsigned)((total + 255) / 256), 256, 0, stream>>>(out, os[0], os[1], os[2], B, D, T);
+        rvq_count_launch(1);
+        return rvq_check_launch("rvq_fill_zero_kernel");
+    }
+    RVQ_REQUIRE(codes && cs, RVQ_EINVAL, "rvq_decode_f32: null codes");
+    RVQ_REQUIRE(code_bytes == 8 || code_bytes == 4, RVQ_EINVAL, "rvq_decode_f32: codes must be int64 or int32");
+    if (code_bytes == 8) return launch_decode<long long>(codes, cs, B, K, T, pv, out, os, status, stream);
+    return launch_decode<int>(codes, cs, B, K, T, pv, out, os, status, stream);
+}

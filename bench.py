@@ -1,0 +1,379 @@
+#!/usr/bin/env python
+"""bench.py -- RVQ encode & decode throughput (BASELINE.json metric) on N B200s of one node.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+A step = one pass of the hot path over one batch of synthetic latents: `encode(x)` followed by
+`decode(codes)` through the drop-in module (audiocraft_b200.quantization.ResidualVectorQuantizer),
+i.e. through the C ABI.  At N = 1 the workload is BASELINE.json configs[1] (MusicGen 32 kHz RVQ,
+n_q=4 bins=2048 dim=128, B=64 x T=1500).  For N > 1 (torchrun, one rank per GPU) every rank
+encodes+decodes its own batch of that shape (frames are independent: weak scaling, no collective
+in the data path) and the codes are all-gathered with NCCL inside the timed region, as
+BASELINE.json configs[4] describes.
+
+Rank 0 prints ONE JSON line.  `value` is frames/s of the whole job with inputs resident in HBM;
+`e2e` is the same through the public API with pinned HOST buffers (H2D of the latents, D2H of
+codes and quantized latents inside the timed region); `roofline` is the encode kernel against the
+measured tensor peak; `cpu_baseline` is the CPU port (oracle/) on the box's host cores.
+
+`--impl reference` times the CPU implementation (the oracle port of the reference algorithm --
+the Python reference itself cannot travel to the GPU box) with every host thread.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "RVQ encode & decode Mframes/s"
+UNIT = "Mframes/s"
+CFG = dict(D=128, C=2048, K=4, B=64, T=1500)  # BASELINE.json configs[1]
+WORKLOAD = "configs[1]: MusicGen 32 kHz EnCodec RVQ n_q=4 bins=2048 dim=128, B=64 x T=1500 frames, encode+decode"
+N_ROTATING = 4  # 4 x 49 MB inputs (197 MB) > 126 MB L2
+
+
+def log(*a):
+    print(*a, file=sys.stderr, flush=True)
+
+
+def measured_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            p = json.load(f)
+        return dict(bf16=float(p["bf16_tflops"]), bf16_sustained=float(p.get("bf16_tflops_sustained", 0) or 0),
+                    hbm=float(p["hbm_gbs"]), source="measured (MEASURED_PEAKS.json)")
+    return dict(bf16=1590.0, bf16_sustained=1400.0, hbm=6650.0, source="fallback (B200_PROFILING.md)")
+
+
+# ------------------------------------------------------------------------------------------------
+# clock sampling during the timed region (NVML; nvidia-smi as a fallback)
+# ------------------------------------------------------------------------------------------------
+class ClockSampler:
+    REASONS = {
+        0x1: "gpu_idle", 0x2: "applications_clocks_setting", 0x4: "sw_power_cap", 0x8: "hw_slowdown",
+        0x10: "sync_boost", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown",
+        0x80: "hw_power_brake_slowdown", 0x100: "display_clock_setting",
+    }
+
+    def __init__(self, index: int):
+        self.index = index
+        self.samples, self.reasons = [], set()
+        self.sm_max = None
+        self._stop = threading.Event()
+        self._thr = None
+        self._nvml = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self._nvml = pynvml
+            # honour CUDA_VISIBLE_DEVICES: map through the PCI bus id of the torch device
+            import torch
+            bus = torch.cuda.get_device_properties(index).pci_bus_id if hasattr(
+                torch.cuda.get_device_properties(index), "pci_bus_id") else None
+            self._h = None
+            if bus is not None:
+                for i in range(pynvml.nvmlDeviceGetCount()):
+                    h = pynvml.nvmlDeviceGetHandleByIndex(i)
+                    if pynvml.nvmlDeviceGetPciInfo(h).bus == bus:
+                        self._h = h
+            if self._h is None:
+                self._h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.sm_max = int(pynvml.nvmlDeviceGetMaxClockInfo(self._h, pynvml.NVML_CLOCK_SM))
+        except Exception as e:  # pragma: no cover
+            log(f"[bench] NVML unavailable ({e}); clocks not sampled")
+            self._nvml = None
+
+    def _run(self):
+        nv = self._nvml
+        while not self._stop.is_set():
+            try:
+                self.samples.append(int(nv.nvmlDeviceGetClockInfo(self._h, nv.NVML_CLOCK_SM)))
+                mask = int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(self._h))
+                for bit, name in self.REASONS.items():
+                    if mask & bit and name != "gpu_idle":
+                        self.reasons.add(name)
+            except Exception:  # pragma: no cover
+                pass
+            time.sleep(0.002)
+
+    def start(self):
+        if self._nvml is not None:
+            self._thr = threading.Thread(target=self._run, daemon=True)
+            self._thr.start()
+
+    def stop(self):
+        if self._thr is not None:
+            self._stop.set()
+            self._thr.join()
+        s = sorted(self.samples)
+        med = s[len(s) // 2] if s else None
+        return {"sm_mhz": med, "sm_max_mhz": self.sm_max, "reasons": sorted(self.reasons), "samples": len(s)}
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU arm: the oracle port of the reference algorithm on the host cores
+# ------------------------------------------------------------------------------------------------
+class CpuPort:
+    """encode+decode of `n_items` x T frames of the bench workload with the CPU port (oracle/)."""
+
+    def __init__(self, n_items: int):
+        import oracle
+        from tests.golden import gen
+        self.oracle = oracle
+        self.embed = gen.codebooks(900, CFG["K"], CFG["C"], CFG["D"])
+        self.x = gen.normalish(901, (n_items, CFG["D"], CFG["T"]))
+        oracle.set_threads(0)
+        self.threads = min(oracle.get_threads(), 64)
+        self.frames = n_items * CFG["T"]
+
+    def one_pass(self) -> float:
+        t0 = time.perf_counter()
+        codes = self.oracle.encode(self.x, self.embed)
+        q = self.oracle.decode(codes, self.embed)
+        dt = time.perf_counter() - t0
+        assert q.shape == self.x.shape
+        return dt
+
+
+def run_reference_arm(args, rank: int):
+    if rank != 0:
+        return 0
+    n_items = 8
+    port = CpuPort(n_items)
+    sample = f"{n_items} of {CFG['B']} batch items ({port.frames} frames) of the workload per step"
+    for _ in range(max(1, args.warmup)):
+        port.one_pass()
+    times = [port.one_pass() for _ in range(args.steps)]
+    total = sum(times)
+    value = port.frames * len(times) / total / 1e6
+    line = {
+        "impl": "reference", "metric": METRIC, "value": round(value, 6), "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(1e3 * total / len(times), 3),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "sample": sample},
+        "cpu_baseline": {"value": round(value, 6), "unit": UNIT, "cores": port.threads, "kind": "port",
+                         "sample": sample},
+        "e2e": {"value": round(value, 6), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+# ------------------------------------------------------------------------------------------------
+# GPU arm
+# ------------------------------------------------------------------------------------------------
+def run_gpu_arm(args, rank: int, world: int, local_rank: int):
+    import torch
+    import torch.distributed as dist
+
+    from audiocraft_b200 import kernels
+    from audiocraft_b200.quantization import ResidualVectorQuantizer
+
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback)"
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    D, C, K, B, T = (CFG[k] for k in "DCKBT")
+    frames = B * T
+    torch.manual_seed(0)
+    m = ResidualVectorQuantizer(dimension=D, n_q=K, bins=C, kmeans_init=False).to(dev).eval()
+    m.vq.check_codes = False  # the in-kernel range check still runs; the host reads the word once, after timing
+    if args.algo:
+        m.vq.encode_algo = args.algo
+    if world > 1:  # codebooks replicated by one broadcast from rank 0
+        for buf in m.buffers():
+            dist.broadcast(buf, src=0)
+    g = torch.Generator(device=dev).manual_seed(1234 + rank)
+    xs = [torch.randn(B, D, T, device=dev, generator=g) for _ in range(N_ROTATING)]
+    gathered = torch.empty((world, K, B, T), dtype=torch.int64, device=dev) if world > 1 else None
+
+    def step(i):
+        x = xs[i % N_ROTATING]
+        codes = m.encode(x)
+        q = m.decode(codes)
+        if world > 1:
+            # codes are a [B, K, T] view of a contiguous [K, B, T] block: gather the block
+            dist.all_gather_into_tensor(gathered, codes.transpose(0, 1))
+        return codes, q
+
+    def sync_all():
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    # ---- device-resident timing -------------------------------------------------------------
+    with torch.no_grad():
+        for i in range(args.warmup):
+            step(i)
+        sync_all()
+        sampler = ClockSampler(local_rank) if rank == 0 else None
+        ev = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(args.steps)]
+        start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        kernels.launch_count(reset=True)
+        if sampler:
+            sampler.start()
+        start.record()
+        for i in range(args.steps):
+            x = xs[i % N_ROTATING]
+            ev[i][0].record()
+            codes = m.encode(x)
+            ev[i][1].record()
+            q = m.decode(codes)
+            ev[i][2].record()
+            if world > 1:
+                dist.all_gather_into_tensor(gathered, codes.transpose(0, 1))
+        end.record()
+        sync_all()
+        launches = kernels.launch_count()
+        clocks = sampler.stop() if sampler else None
+        m.vq.check_errors()
+    elapsed_ms = start.elapsed_time(end)
+    enc_ms = sum(e[0].elapsed_time(e[1]) for e in ev) / args.steps
+    dec_ms = sum(e[1].elapsed_time(e[2]) for e in ev) / args.steps
+    t = torch.tensor([elapsed_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    elapsed_ms = float(t.item())
+
+    # ---- end to end through the public API with host buffers ---------------------------------
+    x_host = [torch.randn(B, D, T).pin_memory() for _ in range(2)]
+    codes_host = torch.empty((B, K, T), dtype=torch.int64).pin_memory()
+    q_host = torch.empty((B, T, D), dtype=torch.float32).pin_memory()
+    x_dev = torch.empty((B, D, T), device=dev)
+
+    def e2e_step(i):
+        x_dev.copy_(x_host[i % 2], non_blocking=True)
+        codes = m.encode(x_dev)
+        q = m.decode(codes)
+        codes_host.copy_(codes, non_blocking=True)
+        q_host.copy_(q.transpose(1, 2), non_blocking=True)  # physical [B, T, D]
+
+    with torch.no_grad():
+        for i in range(min(3, args.warmup)):
+            e2e_step(i)
+        sync_all()
+        s2, e2 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s2.record()
+        for i in range(args.steps):
+            e2e_step(i)
+        e2.record()
+        sync_all()
+    e2e_ms = s2.elapsed_time(e2)
+    t = torch.tensor([e2e_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_ms = float(t.item())
+    h2d = B * D * T * 4
+    d2h = B * K * T * 8 + B * T * D * 4
+
+    # ---- decode on configs[3] (B=256 x T=3000): the HBM-bound yardstick, informational ---------
+    dec_c4 = None
+    if rank == 0 and not args.skip_c4:
+        with torch.no_grad():
+            B4, T4 = 256, 3000
+            cs = [torch.randint(0, C, (B4, K, T4), device=dev) for _ in range(2)]
+            out = None
+            for i in range(3):
+                out = m.decode(cs[i % 2])
+            torch.cuda.synchronize(dev)
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            reps = 20
+            a.record()
+            for i in range(reps):
+                out = m.decode(cs[i % 2])
+            b.record()
+            torch.cuda.synchronize(dev)
+            m.vq.check_errors()
+            us = a.elapsed_time(b) * 1e3 / reps
+            nbytes = B4 * T4 * (8 * K + 4 * D)
+            dec_c4 = {"workload": "configs[3]: decode-only B=256 x T=3000 n_q=4", "us_per_launch": round(us, 2),
+                      "gframes_per_s": round(B4 * T4 / us / 1e3, 3), "achieved_gbs": round(nbytes / us / 1e3, 1)}
+            del cs, out
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return 0
+
+    peaks = measured_peaks()
+    total_frames = frames * world * args.steps
+    value = total_frames / (elapsed_ms * 1e-3) / 1e6
+    enc_flops = 2.0 * D * C * K * frames  # algorithmic: the ||x||^2 - 2 x.c + ||c||^2 contraction only
+    achieved_tf = enc_flops / (enc_ms * 1e-3) / 1e12
+    roofline = {"bound": "tensor", "kernel": "rvq_encode (all stages fused)", "achieved": round(achieved_tf, 3),
+                "peak": peaks["bf16"], "unit": "TFLOP/s", "frac": round(achieved_tf / peaks["bf16"], 5),
+                "traffic": None, "peak_source": peaks["source"] + ", dense bf16 burst",
+                "us_per_launch": round(enc_ms * 1e3, 2)}
+    if dec_c4 is not None:
+        dec_c4["peak_gbs"] = peaks["hbm"]
+        dec_c4["frac"] = round(dec_c4["achieved_gbs"] / peaks["hbm"], 4)
+
+    cpu = None
+    if world == 1 and not args.skip_cpu:
+        port = CpuPort(8)
+        port.one_pass()
+        dt = min(port.one_pass() for _ in range(5))
+        cpu = {"value": round(port.frames / dt / 1e6, 6), "unit": UNIT, "cores": port.threads, "kind": "port",
+               "sample": f"8 of {B} batch items ({port.frames} frames) of the workload, encode+decode, best of 5"}
+
+    line = {
+        "metric": METRIC, "value": round(value, 4), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": round(elapsed_ms / args.steps, 4), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "frames_per_gpu_per_step": frames,
+                   "l2": f"{N_ROTATING} rotating input batches ({N_ROTATING * h2d // 1000000} MB) > 126 MB L2",
+                   "encode_algo": m.vq.encode_algo,
+                   "collective": "all_gather of int64 codes per step" if world > 1 else "none"},
+        "roofline": roofline,
+        "cpu_baseline": cpu,
+        "e2e": {"value": round(frames * world * args.steps / (e2e_ms * 1e-3) / 1e6, 4), "unit": UNIT,
+                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+        "gpu_launches": int(launches),
+        "clocks": clocks,
+        "kernels": {"encode_ms": round(enc_ms, 4), "decode_ms": round(dec_ms, 4),
+                    "encode_mframes_per_s": round(frames / enc_ms / 1e3, 3),
+                    "decode_mframes_per_s": round(frames / dec_ms / 1e3, 3)},
+        "decode_c4": dec_c4,
+    }
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--algo", default="", choices=["", "auto", "exact", "tc"])
+    ap.add_argument("--skip-cpu", action="store_true")
+    ap.add_argument("--skip-c4", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+    if args.impl == "reference":
+        return run_reference_arm(args, rank)
+    if world != args.gpus:
+        log(f"[bench] --gpus {args.gpus} but WORLD_SIZE={world}: launch with torch.distributed.run for N > 1")
+    return run_gpu_arm(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -1,0 +1,95 @@
+/*
+ * rvq_b200.h -- C ABI of librvq_b200.so: the B200 (sm_100a) implementation of the EnCodec
+ * residual-vector-quantization tokenizer path of audiocraft/quantization.
+ *
+ * The reference path is Python (there is no FFI in the reference); every entry point below
+ * names the reference function it replaces.  All pointers marked "device" are CUDA device
+ * pointers on the CURRENT device; `stream` is a cudaStream_t passed as void* (NULL = default
+ * stream).  No entry point allocates device memory: the caller owns every buffer.
+ * Every function returns RVQ_OK (0) or a negative RVQ_E* code; rvq_b200_last_error() then
+ * returns a thread-local, human readable message.  Launch errors are reported by the call that
+ * made the launch; nothing synchronises the device.
+ *
+ * Shapes (names as in the reference): B batch, D `dimension`, T frames, C `bins`,
+ * K active stages (`n_q`), Ktot layers in the module.
+ */
+#ifndef RVQ_B200_H
+#define RVQ_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RVQ_B200_ABI_VERSION 1
+
+#define RVQ_OK 0
+#define RVQ_EINVAL (-1)      /* bad argument (shape, stride, null pointer, size) */
+#define RVQ_EUNSUPPORTED (-2) /* valid for the reference but not implemented here (e.g. D % 4 != 0) */
+#define RVQ_ECUDA (-3)       /* a CUDA runtime / driver call failed */
+#define RVQ_EPACK (-4)       /* `pack` was not produced by rvq_pack_codebooks for these sizes */
+
+#define RVQ_MAX_STAGES 64
+
+/* encode algorithms */
+#define RVQ_ALGO_AUTO 0   /* tensor-core path when the shape allows it, else exact */
+#define RVQ_ALGO_EXACT 1  /* fp32 CUDA-core scan of every code (also the in-kernel fallback) */
+#define RVQ_ALGO_TC 2     /* tcgen05 search + exact fp32 re-score; error if the shape is not covered */
+
+int rvq_b200_abi_version(void);
+const char *rvq_b200_last_error(void);
+
+/*
+ * Codebook pack: private, derived copy of the module's `embed` buffers
+ * (core_vq.py:124-127; state_dict keys vq.layers.{i}._codebook.embed).  Holds the fp32 codebooks
+ * as one [Ktot][C][D] block, ||E_c||^2 per code (replaces the per-call `embed.pow(2).sum(0)` of
+ * core_vq.py:169), fp16 operand copies for the tensor-core search and per-stage metadata.
+ * Must be rebuilt whenever an `embed` buffer changes.
+ */
+int64_t rvq_pack_bytes(int Ktot, int C, int D);
+
+/* embed_ptrs: HOST array of Ktot device pointers, each a contiguous fp32 [C][D] codebook.
+ * pack: device buffer of at least rvq_pack_bytes() bytes, 256-byte aligned. */
+int rvq_pack_codebooks(const float *const *embed_ptrs, int Ktot, int C, int D, void *pack,
+                       int64_t pack_bytes, void *stream);
+
+/*
+ * ResidualVectorQuantization.encode (core_vq.py:387-397), all K stages fused
+ * (EuclideanCodebook.quantize core_vq.py:164-172 + dequantize :177-179 + residual subtract :394).
+ *   pack       built by rvq_pack_codebooks for (Ktot, C, D); the first K <= Ktot stages are used
+ *   x          device fp32, element (b,d,t) at x[b*xs[0] + d*xs[1] + t*xs[2]] (strides in elements)
+ *   codes      device int64 [K][B][T] contiguous -- the torch.stack layout of core_vq.py:396;
+ *              the caller returns codes.transpose(0,1) like vq.py:94
+ *   quantized  NULL, or device fp32 [B][T][D] contiguous receiving 0.0f + q_0 + ... + q_{K-1}
+ *              (eval ResidualVectorQuantization.forward, core_vq.py:363-385)
+ *   workspace  device scratch of rvq_encode_workspace_bytes() bytes (may be NULL when that is 0)
+ */
+int64_t rvq_encode_workspace_bytes(int B, int D, int T, int K, int C, int algo);
+int rvq_encode_f32(const float *x, const int64_t xs[3], int B, int D, int T, const void *pack,
+                   int Ktot, int C, int K, int64_t *codes, float *quantized, void *workspace,
+                   int64_t workspace_bytes, int algo, void *stream);
+
+/*
+ * ResidualVectorQuantization.decode (core_vq.py:399-405; F.embedding gather core_vq.py:177-179):
+ * out = 0.0f + E_0[c_0] + E_1[c_1] + ... in stage order.
+ *   codes      device int64 (code_bytes == 8) or int32 (code_bytes == 4); element (b,k,t) at
+ *              codes[b*cs[0] + k*cs[1] + t*cs[2]] (strides in elements)
+ *   out        device fp32; element (b,d,t) at out[b*os[0] + d*os[1] + t*os[2]].  The reference's
+ *              result is physically [B][T][D], i.e. os = {T*D, 1, D}
+ *   status     device int64[2], zeroed by the caller before the first use.  An out-of-range code
+ *              (the reference raises IndexError) sets status[0] = 1 and status[1] = 1 + the smallest
+ *              flat index (b*K + k)*T + t seen; the frame's output for that stage is skipped.
+ */
+int rvq_decode_f32(const void *codes, int code_bytes, const int64_t cs[3], int B, int K, int T,
+                   const void *pack, int Ktot, int C, int D, float *out, const int64_t os[3],
+                   int64_t *status, void *stream);
+
+/* Introspection used by tests and the bench: number of kernels launched by this library on the
+ * calling thread since the last reset (the bench's `gpu_launches`). */
+int64_t rvq_b200_launch_count(int reset);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RVQ_B200_H */

@@ -56,7 +56,13 @@ def randint(seed: int, shape, high: int) -> np.ndarray:
 
 
 def sha(a: np.ndarray) -> str:
-    return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()[:16]
+    """sha256 of the bytes; NaNs are canonicalised first (their payload/sign differs between
+    x86 and the GPU and carries no meaning)."""
+    a = np.ascontiguousarray(a)
+    if a.dtype.kind == "f" and np.isnan(a).any():
+        a = a.copy()
+        a[np.isnan(a)] = np.float32(np.nan)
+    return hashlib.sha256(a.tobytes()).hexdigest()[:16]
 
 
 # --------------------------------------------------------------------------------------------

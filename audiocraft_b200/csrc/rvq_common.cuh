@@ -14,12 +14,25 @@
 
 #define RVQ_PACK_MAGIC 0x52565142u /* "RVQB" */
 
+// Tensor-core operand image of one 128-code tile of a codebook (D == 128), laid out exactly as the
+// UMMA shared-memory descriptors of rvq_encode_tc.cu read it, so that one 1-D bulk copy brings a tile in:
+//   [0, 16384)      dims   0..63 : 128 rows x 128 B, 16-byte chunks XOR-swizzled with (row & 7)  (SWIZZLE_128B, K-major)
+//   [16384, 32768)  dims 64..127 : same
+//   [32768, 36864)  16 "augmented" K columns: 8x16-byte core matrices, no swizzle
+//                   (row r, chunk c) at (r / 8) * 256 + c * 128 + (r % 8) * 16
+// Values are fp16(E[c][d] * 2^scale_exp); augmented columns 0..2 hold the three-way fp16 split of
+// -(||E_c||^2 / 2) * 2^aug_exp, the rest are zero.
+#define RVQ_TC_TILE_CODES 128
+#define RVQ_TC_IMG_BYTES 36864
+
 // Per-stage metadata written by rvq_pack_codebooks.
 struct RvqStageMeta {
     float cmax_abs;     // max |E[c][d]| over the codebook (finite part)
     float cnorm2_max;   // max ||E_c||^2 (canonical order)
-    int32_t scale_exp;  // fp16 operand copy = E * 2^scale_exp
-    int32_t nonfinite;  // != 0: the codebook holds NaN/Inf -> tensor-core search is not used
+    int32_t scale_exp;  // cmax_abs * 2^scale_exp in [2^13, 2^14)
+    int32_t aug_exp;    // (cnorm2_max / 2) * 2^aug_exp in [2^13, 2^14)
+    int32_t flags;      // bit 0: NaN/Inf in the codebook; bit 1: scale outside the certified range
+    int32_t pad[3];
 };
 
 // First 256 bytes of a pack, followed by the sections at the byte offsets below.
@@ -29,7 +42,7 @@ struct RvqPackHeader {
     int64_t off_meta;   // RvqStageMeta[Ktot]
     int64_t off_embed;  // float [Ktot][C][D]
     int64_t off_cnorm;  // float [Ktot][C]
-    int64_t off_f16;    // __half [Ktot][C][D] (scaled by 2^scale_exp), 0 if absent
+    int64_t off_f16;    // tensor-core images [Ktot][C / 128][RVQ_TC_IMG_BYTES]; empty unless D == 128 and C % 128 == 0
     int64_t total_bytes;
 };
 
@@ -43,7 +56,10 @@ static inline __host__ RvqPackHeader rvq_pack_layout(int Ktot, int C, int D) {
     h.off_meta = off;  off = rvq_align_up(off + (int64_t)sizeof(RvqStageMeta) * Ktot, 256);
     h.off_embed = off; off = rvq_align_up(off + (int64_t)4 * Ktot * C * D, 256);
     h.off_cnorm = off; off = rvq_align_up(off + (int64_t)4 * Ktot * C, 256);
-    h.off_f16 = off;   off = rvq_align_up(off + (int64_t)2 * Ktot * C * D, 1024);
+    off = rvq_align_up(off, 1024);
+    h.off_f16 = off;
+    if (D == 128 && C % RVQ_TC_TILE_CODES == 0) off += (int64_t)Ktot * (C / RVQ_TC_TILE_CODES) * RVQ_TC_IMG_BYTES;
+    off = rvq_align_up(off, 1024);
     h.total_bytes = off;
     return h;
 }
@@ -53,7 +69,7 @@ struct RvqPackView {
     const RvqStageMeta *meta;
     const float *embed;
     const float *cnorm;
-    const __half *f16;
+    const uint8_t *img;  // tensor-core images (see RVQ_TC_IMG_BYTES)
     int Ktot, C, D;
 };
 
@@ -64,7 +80,7 @@ static inline __host__ RvqPackView rvq_pack_view(const void *pack, int Ktot, int
     v.meta = (const RvqStageMeta *)(p + h.off_meta);
     v.embed = (const float *)(p + h.off_embed);
     v.cnorm = (const float *)(p + h.off_cnorm);
-    v.f16 = (const __half *)(p + h.off_f16);
+    v.img = (const uint8_t *)(p + h.off_f16);
     v.Ktot = Ktot; v.C = C; v.D = D;
     return v;
 }

@@ -14,10 +14,24 @@ __device__ __forceinline__ long long load_code(const void *codes, int64_t idx) {
     return (long long)reinterpret_cast<const CodeT *>(codes)[idx];
 }
 
+__device__ __noinline__ void rvq_flag_bad_code(int64_t *status, long long flat) {
+    atomicExch((unsigned long long *)&status[0], 1ull);
+    // keep the smallest flat index; 0 means "none yet"
+    unsigned long long *s1 = (unsigned long long *)&status[1];
+    unsigned long long v = 1ull + (unsigned long long)flat, old = *s1;
+    while (old == 0ull || v < old) {
+        unsigned long long prev = atomicCAS(s1, old, v);
+        if (prev == old) break;
+        old = prev;
+    }
+}
+
+// KT  = K when 1 <= K <= 8 (stage loop fully unrolled, codes of a frame fetched with one or two
+//       128-bit shared loads), 0 = any K (chunks of 8).
 // DCH = D / 128 when D is 128/256/512 (unrolled), else 0 -> generic chunk loop.
-// Dynamic shared memory: int32 codes [warps][K][32] of the 32 frames a warp is working on
-// (-1 = out of range, skipped).
-template <typename CodeT, int DCH>
+// Dynamic shared memory: int32 codes [warps][32 frames][KP] of the 32 frames a warp is working
+// on; an out-of-range code is reported through `status` and replaced by 0.
+template <typename CodeT, int KT, int DCH>
 __global__ void __launch_bounds__(256)
 rvq_decode_kernel(const void *__restrict__ codes, int64_t cs_b, int64_t cs_k, int64_t cs_t, int B, int K, int T,
                   const float *__restrict__ embed, int C, int D, float *__restrict__ out, int64_t os_b,
@@ -26,10 +40,14 @@ rvq_decode_kernel(const void *__restrict__ codes, int64_t cs_b, int64_t cs_k, in
     const int lane = threadIdx.x & 31;
     const int wib = threadIdx.x >> 5;
     const int warps_per_block = blockDim.x >> 5;
-    int *wcodes = s_codes + (size_t)wib * K * 32;
+    const int KP = KT > 0 ? ((KT + 3) & ~3) : ((K + 3) & ~3);  // codes per frame in smem, padded to 4
+    int *wcodes = s_codes + (size_t)wib * KP * 32;
     const int64_t tblocks = (T + 31) / 32;  // 32-frame groups per batch item
     const int64_t ngroups = (int64_t)B * tblocks;
     const int nchunks = DCH > 0 ? DCH : (D + 127) / 128;
+    const int Kc = KT > 0 ? KT : K;
+    const uint32_t row_bytes = (uint32_t)D * 4u;
+    const uint32_t stage_stride = (uint32_t)C * (uint32_t)D;  // elements per codebook (host checks < 2^31)
 
     for (int64_t g = (int64_t)blockIdx.x * warps_per_block + wib; g < ngroups;
          g += (int64_t)gridDim.x * warps_per_block) {
@@ -38,56 +56,76 @@ rvq_decode_kernel(const void *__restrict__ codes, int64_t cs_b, int64_t cs_k, in
         const int nf = min(32, T - t0);
         __syncwarp();
         // lane = frame: coalesced read of the K codes of this lane's frame
-        for (int k = 0; k < K; ++k) {
-            int v = -1;
-            if (lane < nf) {
-                long long c = load_code<CodeT>(codes, b * cs_b + k * cs_k + (int64_t)(t0 + lane) * cs_t);
-                if (c < 0 || c >= C) {
-                    unsigned long long flat = 1ull + (unsigned long long)((b * K + k) * (long long)T + t0 + lane);
-                    atomicExch((unsigned long long *)&status[0], 1ull);
-                    // keep the smallest flat index; 0 means "none yet"
-                    unsigned long long *s1 = (unsigned long long *)&status[1];
-                    unsigned long long old = *s1;
-                    while (old == 0ull || flat < old) {
-                        unsigned long long prev = atomicCAS(s1, old, flat);
-                        if (prev == old) break;
-                        old = prev;
+        if (lane < nf) {
+            const int64_t base = b * cs_b + (int64_t)(t0 + lane) * cs_t;
+#pragma unroll
+            for (int k = 0; k < (KT > 0 ? KT : 1); ++k) {
+                for (int kk = k; kk < Kc; kk += (KT > 0 ? KT : 1)) {
+                    long long c = load_code<CodeT>(codes, base + kk * cs_k);
+                    if (c < 0 || c >= C) {
+                        rvq_flag_bad_code(status, (b * K + kk) * (long long)T + t0 + lane);
+                        c = 0;
                     }
-                } else {
-                    v = (int)c;
+                    wcodes[lane * KP + kk] = (int)c;
                 }
             }
-            wcodes[k * 32 + lane] = v;
         }
         __syncwarp();
         // lane = 4 consecutive dims: walk the frames
+        float *obase = out + b * os_b + (int64_t)t0 * os_t;
         for (int f = 0; f < nf; ++f) {
+            const int *fc = wcodes + f * KP;
             for (int ch = 0; ch < nchunks; ++ch) {
                 const int d = ch * 128 + lane * 4;
                 if (DCH == 0 && d >= D) break;
+                const char *ebase = reinterpret_cast<const char *>(embed + d);
                 float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);  // quantized_out = 0.0 (core_vq.py:400)
-                for (int k0 = 0; k0 < K; k0 += 8) {
-                    float4 row[8];
+                if (KT > 0) {
                     int code[8];
+                    if ((KT & 3) == 0) {
 #pragma unroll
-                    for (int j = 0; j < 8; ++j) {
-                        code[j] = (k0 + j < K) ? wcodes[(k0 + j) * 32 + f] : -1;
-                        row[j] = make_float4(0.f, 0.f, 0.f, 0.f);
-                        if (code[j] >= 0)
-                            row[j] = __ldg(reinterpret_cast<const float4 *>(
-                                embed + ((int64_t)(k0 + j) * C + code[j]) * D + d));
+                        for (int j = 0; j < KT; j += 4) {
+                            int4 v = *reinterpret_cast<const int4 *>(fc + j);
+                            code[j] = v.x; code[j + 1] = v.y; code[j + 2] = v.z; code[j + 3] = v.w;
+                        }
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < KT; ++j) code[j] = fc[j];
                     }
+                    float4 row[8];
 #pragma unroll
-                    for (int j = 0; j < 8; ++j) {
-                        if (code[j] >= 0) {  // stage order (core_vq.py:401-404)
-                            acc.x = __fadd_rn(acc.x, row[j].x);
-                            acc.y = __fadd_rn(acc.y, row[j].y);
-                            acc.z = __fadd_rn(acc.z, row[j].z);
-                            acc.w = __fadd_rn(acc.w, row[j].w);
+                    for (int j = 0; j < KT; ++j)
+                        row[j] = __ldg(reinterpret_cast<const float4 *>(
+                            ebase + (size_t)((uint32_t)j * stage_stride + (uint32_t)code[j] * (uint32_t)D) * 4u));
+#pragma unroll
+                    for (int j = 0; j < KT; ++j) {  // stage order (core_vq.py:401-404)
+                        acc.x = __fadd_rn(acc.x, row[j].x);
+                        acc.y = __fadd_rn(acc.y, row[j].y);
+                        acc.z = __fadd_rn(acc.z, row[j].z);
+                        acc.w = __fadd_rn(acc.w, row[j].w);
+                    }
+                } else {
+                    for (int k0 = 0; k0 < K; k0 += 8) {
+                        float4 row[8];
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            row[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+                            if (k0 + j < K)
+                                row[j] = __ldg(reinterpret_cast<const float4 *>(
+                                    ebase + ((size_t)(k0 + j) * stage_stride + (size_t)fc[k0 + j] * D) * 4u));
+                        }
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            if (k0 + j < K) {
+                                acc.x = __fadd_rn(acc.x, row[j].x);
+                                acc.y = __fadd_rn(acc.y, row[j].y);
+                                acc.z = __fadd_rn(acc.z, row[j].z);
+                                acc.w = __fadd_rn(acc.w, row[j].w);
+                            }
                         }
                     }
                 }
-                float *o = out + b * os_b + (int64_t)(t0 + f) * os_t + (int64_t)d * os_d;
+                float *o = obase + (int64_t)f * os_t + (int64_t)d * os_d;
                 if (os_d == 1) {
                     __stcs(reinterpret_cast<float4 *>(o), acc);  // streaming: keep the codebooks in L2
                 } else {
@@ -95,24 +133,26 @@ rvq_decode_kernel(const void *__restrict__ codes, int64_t cs_b, int64_t cs_k, in
                 }
             }
         }
+        (void)row_bytes;
     }
 }
 
-template <typename CodeT>
-static int launch_decode(const void *codes, const int64_t cs[3], int B, int K, int T, const RvqPackView &pv,
-                         float *out, const int64_t os[3], int64_t *status, cudaStream_t stream) {
+template <typename CodeT, int KT>
+static int launch_decode_k(const void *codes, const int64_t cs[3], int B, int K, int T, const RvqPackView &pv,
+                           float *out, const int64_t os[3], int64_t *status, cudaStream_t stream) {
     const int64_t ngroups = (int64_t)B * ((T + 31) / 32);
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    const int wpb = K <= 32 ? 8 : 4;
-    const size_t smem = (size_t)wpb * K * 32 * sizeof(int);
+    const int KP = (K + 3) & ~3;
+    const int wpb = KP <= 32 ? 8 : 4;
+    const size_t smem = (size_t)wpb * KP * 32 * sizeof(int);
     int64_t blocks = (ngroups + wpb - 1) / wpb;
-    const int64_t cap = (int64_t)sms * 8 * 4;  // grid-stride beyond a few waves of resident CTAs
+    const int64_t cap = (int64_t)sms * 8 * 8;  // grid-stride beyond a few waves of resident CTAs
     if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
 #define RVQ_DEC_LAUNCH(DCH)                                                                              \
-    rvq_decode_kernel<CodeT, DCH><<<(unsigned)blocks, wpb * 32, smem, stream>>>(                         \
+    rvq_decode_kernel<CodeT, KT, DCH><<<(unsigned)blocks, wpb * 32, smem, stream>>>(                     \
         codes, cs[0], cs[1], cs[2], B, K, T, pv.embed, pv.C, pv.D, out, os[0], os[1], os[2], status)
     if (pv.D == 128) RVQ_DEC_LAUNCH(1);
     else if (pv.D == 256) RVQ_DEC_LAUNCH(2);
@@ -121,6 +161,29 @@ static int launch_decode(const void *codes, const int64_t cs[3], int B, int K, i
 #undef RVQ_DEC_LAUNCH
     rvq_count_launch(1);
     return rvq_check_launch("rvq_decode_kernel");
+}
+
+template <typename CodeT>
+static int launch_decode(const void *codes, const int64_t cs[3], int B, int K, int T, const RvqPackView &pv,
+                         float *out, const int64_t os[3], int64_t *status, cudaStream_t stream) {
+    switch (K) {
+        case 1: return launch_decode_k<CodeT, 1>(codes, cs, B, K, T, pv, out, os, status, stream);
+        case 2: return launch_decode_k<CodeT, 2>(codes, cs, B, K, T, pv, out, os, status, stream);
+        case 3: return launch_decode_k<CodeT, 3>(codes, cs, B, K, T, pv, out, os, status, stream);
+        case 4: return launch_decode_k<CodeT, 4>(codes, cs, B, K, T, pv, out, os, status, stream);
+        case 6: return launch_decode_k<CodeT, 6>(codes, cs, B, K, T, pv, out, os, status, stream);
+        case 8: return launch_decode_k<CodeT, 8>(codes, cs, B, K, T, pv, out, os, status, stream);
+        default: return launch_decode_k<CodeT, 0>(codes, cs, B, K, T, pv, out, os, status, stream);
+    }
+}
+
+// Used by the encode path for the eval-forward quantized output: codes [K][B][T] int64 contiguous
+// (just written by the encode kernel) -> out [B][T][D] contiguous.
+int rvq_decode_launch_internal(const int64_t *codes_kbt, int B, int K, int T, const RvqPackView &pv, float *out,
+                               int64_t *status, cudaStream_t stream) {
+    const int64_t cs[3] = {(int64_t)T, (int64_t)B * T, 1};
+    const int64_t os[3] = {(int64_t)T * pv.D, 1, (int64_t)pv.D};
+    return launch_decode<long long>(codes_kbt, cs, B, K, T, pv, out, os, status, stream);
 }
 
 // K == 0: the reference returns the scalar 0.0; the wrapper never calls with K == 0 on a
@@ -146,6 +209,8 @@ extern "C" int rvq_decode_f32(const void *codes, int code_bytes, const int64_t c
     RVQ_REQUIRE(D % 4 == 0, RVQ_EUNSUPPORTED, "rvq_decode_f32: dimension %d is not a multiple of 4", D);
     RVQ_REQUIRE(os[1] != 1 || (((uintptr_t)out & 15) == 0 && os[0] % 4 == 0 && os[2] % 4 == 0), RVQ_EINVAL,
                 "rvq_decode_f32: out must be 16-byte aligned with strides that are multiples of 4");
+    RVQ_REQUIRE((int64_t)Ktot * C * D < ((int64_t)1 << 30), RVQ_EUNSUPPORTED,
+                "rvq_decode_f32: codebooks of %d x %d x %d elements exceed the 32-bit offsets of the kernel", Ktot, C, D);
     RvqPackView pv = rvq_pack_view(pack, Ktot, C, D);
     if (K == 0) {
         int64_t total = (int64_t)B * D * T;

@@ -1,11 +1,602 @@
-// rvq_encode_tc.cu -- tensor-core (tcgen05) search path.  Placeholder until the kernel lands:
-// no shape is reported as supported, so RVQ_ALGO_AUTO resolves to the exact scan.
+// rvq_encode_tc.cu -- ResidualVectorQuantization.encode (core_vq.py:387-397) with the nearest-code
+// search of EuclideanCodebook.quantize (core_vq.py:164-172) on the 5th-generation tensor cores.
+//
+// One persistent CTA per SM, all K stages fused, D == 128.
+//
+//   search (approximate)   acc[frame][code] ~= a * ( r.E_c - ||E_c||^2 / 2 ),  a > 0 per frame:
+//       tcgen05.mma kind::f16, M = 128 frames x N = 128 codes x K = 144 (128 dims + 16 augmented
+//       columns that carry -||E_c||^2/2 as a three-way fp16 split), fp16 operands scaled by powers
+//       of two, fp32 accumulators in TMEM.  Codebook tiles arrive by 1-D bulk copies (UBLKCP) of a
+//       pre-swizzled image (rvq_common.cuh) into a 3-deep ring; the residual operand is written to
+//       shared memory by the warps that own the residual.
+//   scan                   each of 128 threads owns one TMEM lane (= one frame) and reduces the 128
+//       columns of an accumulator in groups of 8 codes.  A group is remembered when its maximum is
+//       within 2*delta of the running maximum, delta being a rigorous bound on |acc - exact|.
+//   resolve (exact)        every remembered group that is within 2*delta of the final maximum is
+//       re-scored in fp32 in the canonical order (rvq_common.cuh), so the emitted code is the one
+//       the exact scan (rvq_encode_exact.cu) emits, bit for bit.  Frames the bound cannot cover
+//       (non-finite values, extreme scales, list overflow) take a full exact scan in place.
+//   then the residual update r -= E_k[code] in registers, the fp16 operand for the next stage.
+//
+// A CTA runs two independent 128-frame tiles ("slots") half a stage apart so that the tensor pipe
+// works on one while the other resolves.  Warp roles (12 warps):
+//   warp 0      producer: decides which slot gets the next codebook tile and streams it in
+//   warp 1      tcgen05.mma issuer, owns the TMEM allocation (512 columns: 2 slots x 2 buffers x 128)
+//   warps 4-7   slot 0: residual owners / scanners / resolvers (warp w owns TMEM lanes 32*(w%4)..)
+//   warps 8-11  slot 1
+#include <limits.h>
+#include <math_constants.h>
+
 #include "rvq_common.cuh"
 
-bool rvq_tc_shape_supported(int D, int C) { (void)D; (void)C; return false; }
-int64_t rvq_tc_workspace_bytes(int B, int D, int T, int K, int C) { (void)B; (void)D; (void)T; (void)K; (void)C; return 0; }
-int rvq_encode_tc(const float *, const int64_t *, int, int, int, const void *, const RvqPackView &, int, int64_t *,
-                  float *, void *, int64_t, cudaStream_t) {
-    rvq_set_error("rvq_encode_tc: not built");
-    return RVQ_EUNSUPPORTED;
+namespace {
+
+constexpr int TILE_M = 128;
+constexpr int NSLOT = 2;
+constexpr int RING = 3;
+constexpr int IMG = RVQ_TC_IMG_BYTES;  // 36864: kb0 | kb1 | aug
+constexpr int LISTCAP = 16;
+constexpr int THREADS = 384;
+
+// shared memory map (offsets from a 1024-byte aligned base)
+constexpr int SM_RING = 0;
+constexpr int SM_A = SM_RING + RING * IMG;                 // 110592
+constexpr int SM_LIST = SM_A + NSLOT * IMG;                // 184320
+constexpr int SM_BAR = SM_LIST + NSLOT * LISTCAP * TILE_M * 4;  // 200704
+constexpr int SM_TOTAL = SM_BAR + 256;
+constexpr int SM_ALLOC = SM_TOTAL + 1024;                  // slack for manual alignment
+
+// barrier indices (8 bytes each)
+constexpr int BAR_BFULL = 0;                    // [RING]
+constexpr int BAR_BEMPTY = BAR_BFULL + RING;    // [RING]
+constexpr int BAR_ACCFULL = BAR_BEMPTY + RING;  // [NSLOT][2]
+constexpr int BAR_ACCEMPTY = BAR_ACCFULL + 4;   // [NSLOT][2]
+constexpr int BAR_AREADY = BAR_ACCEMPTY + 4;    // [NSLOT]
+constexpr int BAR_COUNT = BAR_AREADY + NSLOT;   // 16
+constexpr int SM_META = SM_BAR + BAR_COUNT * 8; // ring_meta[RING] (u32), tmem base (u32)
+
+// instruction descriptor: kind::f16, A = B = F16, D = F32, both K-major, M = 128, N = 128
+constexpr uint32_t IDESC = (1u << 4) | ((128u >> 3) << 17) | ((128u >> 4) << 24);
+
+// ------------------------------------------------------------------------------------ PTX
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ bool mbar_test(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    while (!mbar_test(bar, parity)) {}
+}
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+                 "l"(src), "r"(bytes), "r"(bar)
+                 : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+__device__ __forceinline__ void umma_f16(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+        "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc)
+        : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+          "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),
+          "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
+          "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+        : "r"(taddr)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// K-major SWIZZLE_128B operand: rows of 128 bytes, 8-row groups 1024 bytes apart (SBO), version 1
+__device__ __forceinline__ uint64_t desc_sw128(uint32_t saddr) {
+    return (uint64_t)((saddr & 0x3FFFFu) >> 4) | ((uint64_t)1 << 16) | ((uint64_t)(1024 >> 4) << 32) | ((uint64_t)1 << 46) |
+           ((uint64_t)2 << 61);
+}
+// K-major, no swizzle: 8x16-byte core matrices; the two K chunks 128 bytes apart (LBO), 8-row groups 256 bytes apart (SBO)
+__device__ __forceinline__ uint64_t desc_interleaved(uint32_t saddr) {
+    return (uint64_t)((saddr & 0x3FFFFu) >> 4) | ((uint64_t)(128 >> 4) << 16) | ((uint64_t)(256 >> 4) << 32) |
+           ((uint64_t)1 << 46);
+}
+
+// ------------------------------------------------------------------------------------ exact helpers
+// In place: p[0..31] (this lane's partials of 32 columns) -> p[0] = canonical sum of column `lane`.
+__device__ __forceinline__ void transposed_butterfly32(float (&p)[32], int lane) {
+#pragma unroll
+    for (int half = 16; half >= 1; half >>= 1) {
+        const bool up = (lane & half) != 0;
+#pragma unroll
+        for (int i = 0; i < half; ++i) {
+            float send = up ? p[i] : p[i + half];
+            float keep = up ? p[i + half] : p[i];
+            p[i] = __fadd_rn(keep, __shfl_xor_sync(0xffffffffu, send, half));
+        }
+    }
+}
+// 8 columns: after the three halving rounds lane l holds column (l >> 2) & 7; two plain rounds finish it.
+__device__ __forceinline__ float transposed_butterfly8(float (&p)[8], int lane) {
+#pragma unroll
+    for (int half = 4; half >= 1; half >>= 1) {
+        const int off = half * 4;  // lane distance 16, 8, 4
+        const bool up = (lane & off) != 0;
+#pragma unroll
+        for (int i = 0; i < half; ++i) {
+            float send = up ? p[i] : p[i + half];
+            float keep = up ? p[i + half] : p[i];
+            p[i] = __fadd_rn(keep, __shfl_xor_sync(0xffffffffu, send, off));
+        }
+    }
+    float v = p[0];
+    v = __fadd_rn(v, __shfl_xor_sync(0xffffffffu, v, 2));
+    v = __fadd_rn(v, __shfl_xor_sync(0xffffffffu, v, 1));
+    return v;
+}
+
+__device__ __forceinline__ void warp_argmax(float &bs, int &bi) {
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) {
+        float os = __shfl_xor_sync(0xffffffffu, bs, off);
+        int oi = __shfl_xor_sync(0xffffffffu, bi, off);
+        if (rvq_better(os, oi, bs, bi)) { bs = os; bi = oi; }
+    }
+}
+
+// Full exact scan of one frame by one warp (lane owns dims 4*lane..4*lane+3).  Same arithmetic as
+// rvq_encode_exact.cu.  Used for frames the certified search cannot cover.
+__device__ __noinline__ int exact_scan_frame(float4 rf, float xx, const float *__restrict__ Ek,
+                                             const float *__restrict__ cnk, int C, int lane) {
+    float best = -CUDART_INF_F;
+    int bidx = INT_MAX;
+    for (int c0 = 0; c0 < C; c0 += 32) {
+        float p[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+            const float4 e = __ldg(reinterpret_cast<const float4 *>(Ek + (size_t)(c0 + j) * 128) + lane);
+            float a = __fmaf_rn(rf.x, e.x, 0.0f);
+            a = __fmaf_rn(rf.y, e.y, a);
+            a = __fmaf_rn(rf.z, e.z, a);
+            p[j] = __fmaf_rn(rf.w, e.w, a);
+        }
+        transposed_butterfly32(p, lane);
+        const int col = c0 + lane;
+        const float s = rvq_score(xx, p[0], cnk[col]);
+        if (rvq_better(s, col, best, bidx)) { best = s; bidx = col; }
+    }
+    warp_argmax(best, bidx);
+    return bidx;
+}
+
+// Exact resolution of one frame: re-score the remembered groups that can still hold the winner.
+// list: this frame's entries, entry e at list[e * TILE_M]; entry = (float bits & ~0x7FF) | group.
+__device__ __noinline__ int resolve_frame(float4 rf, float xx, int cnt, float M, float twodelta, int flags,
+                                          const uint32_t *list, const float *__restrict__ Ek,
+                                          const float *__restrict__ cnk, int C, int lane) {
+    int idx;
+    if (flags != 0 || cnt > LISTCAP) {
+        idx = exact_scan_frame(rf, xx, Ek, cnk, C, lane);
+    } else {
+        // entries were stored with 11 mantissa bits cleared: allow for that when filtering
+        const float thr = M - twodelta - 0.0009765625f * (fabsf(M) + twodelta);
+        float best = -CUDART_INF_F;
+        int bidx = INT_MAX;
+        for (int e = 0; e < cnt; ++e) {
+            const uint32_t u = list[e * TILE_M];
+            const float val = __uint_as_float(u & ~0x7FFu);
+            if (!(val >= thr)) continue;  // warp uniform
+            const int c0 = (int)(u & 0x7FFu) * 8;
+            float p[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const float4 ev = __ldg(reinterpret_cast<const float4 *>(Ek + (size_t)(c0 + j) * 128) + lane);
+                float a = __fmaf_rn(rf.x, ev.x, 0.0f);
+                a = __fmaf_rn(rf.y, ev.y, a);
+                a = __fmaf_rn(rf.z, ev.z, a);
+                p[j] = __fmaf_rn(rf.w, ev.w, a);
+            }
+            const float dot = transposed_butterfly8(p, lane);
+            const int col = c0 + ((lane >> 2) & 7);
+            const float s = rvq_score(xx, dot, cnk[col]);
+            if (rvq_better(s, col, best, bidx)) { best = s; bidx = col; }
+        }
+        warp_argmax(best, bidx);
+        idx = bidx;
+        if (idx == INT_MAX) idx = exact_scan_frame(rf, xx, Ek, cnk, C, lane);  // cannot happen; stay total
+    }
+    return idx;
+}
+
+struct TcParams {
+    const float *x;
+    int64_t xs_b, xs_d, xs_t;
+    int B, T;
+    int64_t N;            // frames
+    int ntiles;           // ceil(N / 128)
+    const uint8_t *img;   // [Ktot][NT][IMG]
+    const float *embed;   // [Ktot][C][128]
+    const float *cnorm;   // [Ktot][C]
+    const RvqStageMeta *meta;
+    int C, K, NT;         // NT = C / 128
+    int64_t *codes;       // [K][N]
+    // diagnostics (optional): accumulators and per-frame scan state of CTA 0 / slot 0 / first tile
+    float *dbg_acc;       // [128][C] raw accumulators of stage dbg_stage
+    float *dbg_info;      // [128][8]
+    int dbg_stage;
+};
+
+__device__ __forceinline__ int slot_tiles(int ntiles, int grid, int cta, int slot) {
+    // slot s of CTA c owns tiles c + grid * (s + 2 m)
+    const int first = cta + grid * slot;
+    if (first >= ntiles) return 0;
+    return (ntiles - first + 2 * grid - 1) / (2 * grid);
+}
+
+// ------------------------------------------------------------------------------------ kernel
+__global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParams P) {
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    uint8_t *sm = smem_raw + (base - smem_u32(smem_raw));
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t bar0 = base + SM_BAR;
+    auto BAR = [&](int i) { return bar0 + 8u * (uint32_t)i; };
+    volatile uint32_t *ring_meta = reinterpret_cast<volatile uint32_t *>(sm + SM_META);
+    volatile uint32_t *tmem_slot = reinterpret_cast<volatile uint32_t *>(sm + SM_META + 16);
+
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < RING; ++i) { mbar_init(BAR(BAR_BFULL + i), 1); mbar_init(BAR(BAR_BEMPTY + i), 1); }
+        for (int i = 0; i < 4; ++i) { mbar_init(BAR(BAR_ACCFULL + i), 1); mbar_init(BAR(BAR_ACCEMPTY + i), 4); }
+        for (int i = 0; i < NSLOT; ++i) mbar_init(BAR(BAR_AREADY + i), 4);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32((void *)tmem_slot)),
+                     "r"(512u)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot;
+
+    const int grid = gridDim.x, cta = blockIdx.x;
+    const int NT = P.NT, K = P.K;
+    const int per_tile = K * NT;  // items per tile
+
+    if (warp < 4) {
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+        if (warp == 0 && lane == 0) {
+            // ============================ producer ============================
+            const int total0 = slot_tiles(P.ntiles, grid, cta, 0) * per_tile;
+            const int total1 = slot_tiles(P.ntiles, grid, cta, 1) * per_tile;
+            const int lead = min(NT / 2, total0);  // slot 1 starts half a stage behind slot 0
+            int next0 = 0, next1 = 0, it = 0, last = 1;
+            while (next0 < total0 || next1 < total1) {
+                int s = -1;
+#pragma unroll
+                for (int attempt = 0; attempt < 2; ++attempt) {
+                    const int cand = attempt == 0 ? (last ^ 1) : last;
+                    const int nx = cand ? next1 : next0;
+                    const int tot = cand ? total1 : total0;
+                    if (s >= 0 || nx >= tot) continue;
+                    if (cand == 1 && next1 == 0 && next0 < lead) continue;
+                    if (nx % NT == 0 && !mbar_test(BAR(BAR_AREADY + cand), (uint32_t)(nx / NT) & 1u)) continue;
+                    s = cand;
+                }
+                if (s < 0) { __nanosleep(32); continue; }
+                const int ridx = it % RING;
+                mbar_wait(BAR(BAR_BEMPTY + ridx), (((uint32_t)(it / RING)) & 1u) ^ 1u);
+                ring_meta[ridx] = (uint32_t)s;
+                const int i = s ? next1 : next0;
+                const int k = (i / NT) % K, j = i % NT;
+                mbar_arrive_expect_tx(BAR(BAR_BFULL + ridx), IMG);
+                bulk_g2s(base + SM_RING + ridx * IMG, P.img + ((size_t)k * NT + j) * IMG, IMG, BAR(BAR_BFULL + ridx));
+                if (s) ++next1; else ++next0;
+                last = s;
+                ++it;
+            }
+        } else if (warp == 1 && lane == 0) {
+            // ============================ MMA issuer ============================
+            const int total = (slot_tiles(P.ntiles, grid, cta, 0) + slot_tiles(P.ntiles, grid, cta, 1)) * per_tile;
+            int cnt0 = 0, cnt1 = 0;
+            for (int it = 0; it < total; ++it) {
+                const int ridx = it % RING;
+                mbar_wait(BAR(BAR_BFULL + ridx), ((uint32_t)(it / RING)) & 1u);
+                const int s = (int)ring_meta[ridx];
+                const int c = s ? cnt1 : cnt0;
+                if (c % NT == 0) mbar_wait(BAR(BAR_AREADY + s), (uint32_t)(c / NT) & 1u);
+                const int buf = c & 1;
+                mbar_wait(BAR(BAR_ACCEMPTY + s * 2 + buf), (((uint32_t)(c >> 1)) & 1u) ^ 1u);
+                tc_fence_after();
+                const uint32_t d = tmem + (uint32_t)(s * 256 + buf * 128);
+                const uint32_t a = base + SM_A + s * IMG, b = base + SM_RING + ridx * IMG;
+#pragma unroll
+                for (int kb = 0; kb < 2; ++kb)
+#pragma unroll
+                    for (int ks = 0; ks < 4; ++ks)
+                        umma_f16(d, desc_sw128(a + kb * 16384 + ks * 32), desc_sw128(b + kb * 16384 + ks * 32), IDESC,
+                                 (kb | ks) ? 1u : 0u);
+                umma_f16(d, desc_interleaved(a + 32768), desc_interleaved(b + 32768), IDESC, 1u);
+                umma_commit(BAR(BAR_BEMPTY + ridx));
+                umma_commit(BAR(BAR_ACCFULL + s * 2 + buf));
+                if (s) ++cnt1; else ++cnt0;
+            }
+        }
+    } else {
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
+        // ============================ frame warps ============================
+        const int slot = (warp - 4) >> 2, q = warp & 3;
+        uint8_t *A = sm + SM_A + slot * IMG;
+        uint32_t *list = reinterpret_cast<uint32_t *>(sm + SM_LIST) + slot * LISTCAP * TILE_M;
+        const int row_l = q * 32 + lane;  // the row (frame of the tile) this thread scans
+        const int C = P.C;
+        uint32_t items = 0;  // accumulator uses of this slot so far
+
+        for (int tile = cta + grid * slot, first = 1; tile < P.ntiles; tile += 2 * grid, first = 0) {
+            const int64_t n0 = (int64_t)tile * TILE_M + q * 32;
+            // ---- residual: lane owns dims 4*lane..4*lane+3 of each of the warp's 32 frames
+            float4 r[32];
+            if (P.xs_d == 1 && (P.xs_b & 3) == 0 && (P.xs_t & 3) == 0 && ((uintptr_t)P.x & 15) == 0) {
+#pragma unroll
+                for (int f = 0; f < 32; ++f) {
+                    const int64_t n = n0 + f;
+                    r[f] = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (n < P.N)
+                        r[f] = *reinterpret_cast<const float4 *>(P.x + (n / P.T) * P.xs_b + (n % P.T) * P.xs_t + 4 * lane);
+                }
+            } else {
+                // lane = frame reads (coalesced when T is the contiguous axis), transposed through this
+                // warp's own 4 KB of the A tile, 32 dims at a time
+                const int64_t n = n0 + lane;
+                const bool valid = n < P.N;
+                const float *xp = P.x + (valid ? (n / P.T) * P.xs_b + (n % P.T) * P.xs_t : 0);
+                float *st = reinterpret_cast<float *>(A + q * 4096);
+#pragma unroll
+                for (int pass = 0; pass < 4; ++pass) {
+                    __syncwarp();
+#pragma unroll 8
+                    for (int dd = 0; dd < 32; ++dd)
+                        st[dd * 32 + (lane ^ dd)] = valid ? xp[(int64_t)(pass * 32 + dd) * P.xs_d] : 0.0f;
+                    __syncwarp();
+                    if ((lane >> 3) == pass) {
+                        const int dl = 4 * (lane & 7);
+#pragma unroll
+                        for (int f = 0; f < 32; ++f) {
+                            r[f].x = st[(dl + 0) * 32 + (f ^ (dl + 0))];
+                            r[f].y = st[(dl + 1) * 32 + (f ^ (dl + 1))];
+                            r[f].z = st[(dl + 2) * 32 + (f ^ (dl + 2))];
+                            r[f].w = st[(dl + 3) * 32 + (f ^ (dl + 3))];
+                        }
+                    }
+                }
+                __syncwarp();
+            }
+
+            for (int k = 0; k < K; ++k) {
+                const float *Ek = P.embed + (size_t)k * C * 128;
+                const float *cnk = P.cnorm + (size_t)k * C;
+                const RvqStageMeta mt = P.meta[k];
+                // ---- ||r||^2 of the 32 frames in canonical order; lane f ends up with frame f's
+                float xx;
+                {
+                    float p[32];
+#pragma unroll
+                    for (int f = 0; f < 32; ++f) {
+                        float a = __fmaf_rn(r[f].x, r[f].x, 0.0f);
+                        a = __fmaf_rn(r[f].y, r[f].y, a);
+                        a = __fmaf_rn(r[f].z, r[f].z, a);
+                        p[f] = __fmaf_rn(r[f].w, r[f].w, a);
+                    }
+                    transposed_butterfly32(p, lane);
+                    xx = p[0];
+                }
+                // ---- per-frame scaling and error bound (this thread's frame = lane)
+                int flags = mt.flags ? 4 : 0;
+                int ea = 0;
+                if (!(xx <= 3.0e38f)) flags |= 1;  // NaN or Inf
+                if (xx > 0.0f && flags == 0) {
+                    int e2;
+                    frexpf(xx, &e2);        // xx = m * 2^e2, m in [0.5, 1)  ->  ||r|| <= 2^ceil(e2/2)
+                    ea = -((e2 + 1) >> 1);  // alpha * ||r|| in (0.35, 1]
+                }
+                const int aexp = ea + mt.scale_exp - mt.aug_exp;
+                if (aexp < -24 || aexp > 15) flags |= 2;
+                const float alpha = flags ? 0.0f : ldexpf(1.0f, ea);
+                const float scale_acc = ldexpf(1.0f, ea + mt.scale_exp);  // acc ~= scale_acc * (r.c - cc/2)
+                const float R = sqrtf(xx), cn_max = sqrtf(mt.cnorm2_max);
+                const float e16 = 0.0009765625f * scale_acc * R * cn_max;          // 2^-10: fp16 rounding of both operands
+                const float e32 = 2.384185791015625e-07f * (xx + 2.0f * R * cn_max + mt.cnorm2_max) +
+                                  3.814697265625e-06f * R * cn_max;                 // canonical fp32 evaluation
+                const float twodelta = 2.0002f * (1.2505f * e16 + 0.5f * scale_acc * e32 + 1.0f);
+                const __half a_aug = __float2half_rn(flags ? 0.0f : ldexpf(1.0f, aexp));
+
+                // ---- fp16 operand rows of this warp's frames (SWIZZLE_128B image, see rvq_common.cuh)
+#pragma unroll
+                for (int f = 0; f < 32; ++f) {
+                    const float al = __shfl_sync(0xffffffffu, alpha, f);
+                    const __half2 h0 = __floats2half2_rn(r[f].x * al, r[f].y * al);
+                    const __half2 h1 = __floats2half2_rn(r[f].z * al, r[f].w * al);
+                    const int row = q * 32 + f;
+                    const int off = (lane >> 4) * 16384 + row * 128 + ((((lane & 15) >> 1) ^ (f & 7)) << 4) + (lane & 1) * 8;
+                    uint2 w;
+                    w.x = *reinterpret_cast<const uint32_t *>(&h0);
+                    w.y = *reinterpret_cast<const uint32_t *>(&h1);
+                    *reinterpret_cast<uint2 *>(A + off) = w;
+                }
+                {
+                    const uint32_t h = (uint32_t)__half_as_ushort(a_aug);
+                    uint8_t *ar = A + 32768 + (row_l >> 3) * 256 + (row_l & 7) * 16;
+                    *reinterpret_cast<uint4 *>(ar) = make_uint4(h | (h << 16), h, 0u, 0u);
+                    *reinterpret_cast<uint4 *>(ar + 128) = make_uint4(0u, 0u, 0u, 0u);
+                }
+                fence_proxy_async();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(BAR(BAR_AREADY + slot));
+
+                // ---- scan: this thread's frame = TMEM lane row_l
+                float M = -CUDART_INF_F, thr = -CUDART_INF_F;
+                int cnt = 0;
+                const bool dbg = P.dbg_acc != nullptr && cta == 0 && slot == 0 && first && k == P.dbg_stage;
+                for (int j = 0; j < NT; ++j, ++items) {
+                    const int buf = items & 1;
+                    mbar_wait(BAR(BAR_ACCFULL + slot * 2 + buf), (items >> 1) & 1u);
+                    tc_fence_after();
+                    const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(slot * 256 + buf * 128);
+#pragma unroll 1
+                    for (int ch = 0; ch < 4; ++ch) {
+                        uint32_t v[32];
+                        tmem_ld32(taddr + ch * 32, v);
+                        tmem_wait_ld();
+                        if (dbg) {
+#pragma unroll
+                            for (int i = 0; i < 32; ++i)
+                                P.dbg_acc[(size_t)row_l * C + j * 128 + ch * 32 + i] = __uint_as_float(v[i]);
+                        }
+#pragma unroll
+                        for (int g = 0; g < 4; ++g) {
+                            float gm = fmaxf(fmaxf(__uint_as_float(v[8 * g]), __uint_as_float(v[8 * g + 1])),
+                                             fmaxf(__uint_as_float(v[8 * g + 2]), __uint_as_float(v[8 * g + 3])));
+                            gm = fmaxf(gm, fmaxf(fmaxf(__uint_as_float(v[8 * g + 4]), __uint_as_float(v[8 * g + 5])),
+                                                 fmaxf(__uint_as_float(v[8 * g + 6]), __uint_as_float(v[8 * g + 7]))));
+                            if (gm >= thr) {
+                                if (cnt < LISTCAP)
+                                    list[cnt * TILE_M + row_l] = (__float_as_uint(gm) & ~0x7FFu) | (uint32_t)(j * 16 + ch * 4 + g);
+                                ++cnt;
+                            }
+                            M = fmaxf(M, gm);
+                            thr = M - twodelta;
+                        }
+                    }
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(BAR(BAR_ACCEMPTY + slot * 2 + buf));
+                }
+                if (dbg) {
+                    float *o = P.dbg_info + row_l * 8;
+                    o[0] = xx; o[1] = alpha; o[2] = twodelta; o[3] = M; o[4] = (float)cnt; o[5] = (float)flags;
+                    o[6] = scale_acc; o[7] = __half2float(a_aug);
+                }
+                __syncwarp();  // the lists written by lane = frame are read by every lane below
+
+                // ---- resolve, frame by frame (warp cooperative), then the coalesced code store
+                int mycode = 0;
+#pragma unroll
+                for (int f = 0; f < 32; ++f) {
+                    const float xf = __shfl_sync(0xffffffffu, xx, f);
+                    const int cf = __shfl_sync(0xffffffffu, cnt, f);
+                    const float Mf = __shfl_sync(0xffffffffu, M, f);
+                    const float tf = __shfl_sync(0xffffffffu, twodelta, f);
+                    const int ff = __shfl_sync(0xffffffffu, flags, f);
+                    const int idx = resolve_frame(r[f], xf, cf, Mf, tf, ff, list + q * 32 + f, Ek, cnk, C, lane);
+                    if (lane == f) mycode = idx;
+                    // residual = residual - quantized (core_vq.py:394)
+                    const float4 w = __ldg(reinterpret_cast<const float4 *>(Ek + (size_t)idx * 128) + lane);
+                    r[f].x = __fsub_rn(r[f].x, w.x);
+                    r[f].y = __fsub_rn(r[f].y, w.y);
+                    r[f].z = __fsub_rn(r[f].z, w.z);
+                    r[f].w = __fsub_rn(r[f].w, w.w);
+                }
+                if (n0 + lane < P.N) P.codes[(int64_t)k * P.N + n0 + lane] = (int64_t)mycode;
+                __syncwarp();
+            }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512u) : "memory");
+    }
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------ host
+bool rvq_tc_shape_supported(int D, int C) { return D == 128 && C % 128 == 0 && C >= 256 && C <= 16384; }
+
+int64_t rvq_tc_workspace_bytes(int B, int D, int T, int K, int C) {
+    (void)B; (void)D; (void)T; (void)K; (void)C;
+    return 256;  // the decode status word used when the quantized output is requested
+}
+
+int rvq_decode_launch_internal(const int64_t *codes_kbt, int B, int K, int T, const RvqPackView &pv, float *out,
+                               int64_t *status, cudaStream_t stream);
+
+static int launch_tc(const float *x, const int64_t xs[3], int B, int T, const RvqPackView &pv, int K, int64_t *codes,
+                     float *dbg_acc, float *dbg_info, int dbg_stage, cudaStream_t stream) {
+    TcParams P;
+    P.x = x; P.xs_b = xs[0]; P.xs_d = xs[1]; P.xs_t = xs[2];
+    P.B = B; P.T = T; P.N = (int64_t)B * T;
+    RVQ_REQUIRE(P.N <= (int64_t)INT_MAX / 2, RVQ_EUNSUPPORTED, "rvq_encode_f32: too many frames for one call");
+    P.ntiles = (int)((P.N + TILE_M - 1) / TILE_M);
+    P.img = pv.img; P.embed = pv.embed; P.cnorm = pv.cnorm; P.meta = pv.meta;
+    P.C = pv.C; P.K = K; P.NT = pv.C / 128;
+    P.codes = codes;
+    P.dbg_acc = dbg_acc; P.dbg_info = dbg_info; P.dbg_stage = dbg_stage;
+    int dev = 0, sms = 148;
+    RVQ_CUDA(cudaGetDevice(&dev));
+    RVQ_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    int grid = (P.ntiles + NSLOT - 1) / NSLOT;
+    if (grid > sms) grid = sms;
+    static bool attr_set[64] = {false};
+    if (dev < 64 && !attr_set[dev]) {
+        RVQ_CUDA(cudaFuncSetAttribute(rvq_encode_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_ALLOC));
+        attr_set[dev] = true;
+    }
+    rvq_encode_tc_kernel<<<grid, THREADS, SM_ALLOC, stream>>>(P);
+    rvq_count_launch(1);
+    return rvq_check_launch("rvq_encode_tc_kernel");
+}
+
+int rvq_encode_tc(const float *x, const int64_t xs[3], int B, int D, int T, const void *pack, const RvqPackView &pv,
+                  int K, int64_t *codes, float *quantized, void *workspace, int64_t workspace_bytes,
+                  cudaStream_t stream) {
+    (void)pack; (void)D;
+    RVQ_REQUIRE(!quantized || (workspace && workspace_bytes >= 16), RVQ_EINVAL,
+                "rvq_encode_f32: workspace of rvq_encode_workspace_bytes() bytes required");
+    int rc = launch_tc(x, xs, B, T, pv, K, codes, nullptr, nullptr, 0, stream);
+    if (rc != RVQ_OK || !quantized) return rc;
+    // quantized_out = 0 + q_0 + ... (core_vq.py:363-385): the gather-sum kernel on the codes just written
+    RVQ_CUDA(cudaMemsetAsync(workspace, 0, 16, stream));
+    return rvq_decode_launch_internal(codes, B, K, T, pv, quantized, (int64_t *)workspace, stream);
+}
+
+// Diagnostics: raw tensor-core accumulators and scan state of the first 128 frames, stage `stage`.
+extern "C" int rvq_debug_tc_scores(const float *x, const int64_t xs[3], int B, int D, int T, const void *pack, int Ktot,
+                                   int C, int K, int stage, int64_t *codes, float *acc_out, float *info_out,
+                                   void *stream_) {
+    RVQ_REQUIRE(x && xs && pack && codes && acc_out && info_out, RVQ_EINVAL, "rvq_debug_tc_scores: null pointer");
+    RVQ_REQUIRE(rvq_tc_shape_supported(D, C) && K > 0 && K <= Ktot && stage >= 0 && stage < K, RVQ_EUNSUPPORTED,
+                "rvq_debug_tc_scores: shape not covered by the tensor-core path");
+    RvqPackView pv = rvq_pack_view(pack, Ktot, C, D);
+    return launch_tc(x, xs, B, T, pv, K, codes, acc_out, info_out, stage, (cudaStream_t)stream_);
 }

@@ -79,42 +79,65 @@ __global__ void __launch_bounds__(256) rvq_cnorm_kernel(const float *__restrict_
         // non-negative floats order like their bit patterns
         atomicMax((int *)&m->cmax_abs, __float_as_int(amax));
         if (p <= 3.0e38f) atomicMax((int *)&m->cnorm2_max, __float_as_int(p)); else bad = 1;
-        if (bad) atomicOr(&m->nonfinite, 1);
+        if (bad) atomicOr(&m->flags, 1);
     }
 }
 
-// scale_exp: cmax_abs * 2^scale_exp in [2^14, 2^15)  (0 for an all-zero codebook)
+// scale_exp / aug_exp: put the largest operand of each kind at [2^13, 2^14) in fp16
 __global__ void rvq_scale_kernel(RvqStageMeta *__restrict__ meta, int Ktot) {
     int k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= Ktot) return;
+    int flags = meta[k].flags;
+    int e = 0, ea = 0, ex;
     float a = meta[k].cmax_abs;
-    int e = 0;
-    if (a > 0.0f) {
-        int ex;
-        frexpf(a, &ex);  // a = m * 2^ex, m in [0.5, 1) -> a in [2^(ex-1), 2^ex)
-        e = 15 - ex;
-    }
-    if (e > 60 || e < -60) {  // outside the range the fp16 search is certified for
-        atomicOr(&meta[k].nonfinite, 2);
-        e = max(-60, min(60, e));
+    if (a > 0.0f) { frexpf(a, &ex); e = 14 - ex; }   // a in [2^(ex-1), 2^ex)
+    float h = 0.5f * meta[k].cnorm2_max;
+    if (h > 0.0f) { frexpf(h, &ex); ea = 14 - ex; }
+    if (e > 40 || e < -40 || ea > 40 || ea < -40) {  // outside the range the fp16 search is certified for
+        flags |= 2;
+        e = max(-40, min(40, e));
+        ea = max(-40, min(40, ea));
     }
     meta[k].scale_exp = e;
+    meta[k].aug_exp = ea;
+    meta[k].flags = flags;
 }
 
-__global__ void __launch_bounds__(256) rvq_f16_kernel(const float *__restrict__ embed, int64_t per_stage,
-                                                      int64_t total, const RvqStageMeta *__restrict__ meta,
-                                                      __half *__restrict__ out) {
-    int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+// One thread per 16-byte chunk of the tensor-core image: 18 chunks per code (16 data + 2 augmented).
+__global__ void __launch_bounds__(256) rvq_image_kernel(const float *__restrict__ embed, const float *__restrict__ cnorm,
+                                                        int Ktot, int C, const RvqStageMeta *__restrict__ meta,
+                                                        uint8_t *__restrict__ img) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t total = (int64_t)Ktot * C * 18;
     if (i >= total) return;
-    int k = (int)(i / per_stage);
-    float s = ldexpf(1.0f, meta[k].scale_exp);
-    float4 v = *reinterpret_cast<const float4 *>(embed + i);
-    __half2 lo = __floats2half2_rn(v.x * s, v.y * s);
-    __half2 hi = __floats2half2_rn(v.z * s, v.w * s);
-    uint2 o;
-    o.x = *reinterpret_cast<uint32_t *>(&lo);
-    o.y = *reinterpret_cast<uint32_t *>(&hi);
-    *reinterpret_cast<uint2 *>(out + i) = o;
+    const int chunk = (int)(i % 18);
+    const int64_t kc = i / 18;
+    const int k = (int)(kc / C), c = (int)(kc % C);
+    const int tile = c / RVQ_TC_TILE_CODES, r = c % RVQ_TC_TILE_CODES;
+    uint8_t *base = img + ((int64_t)k * (C / RVQ_TC_TILE_CODES) + tile) * RVQ_TC_IMG_BYTES;
+    __half v[8];
+    size_t off;
+    if (chunk < 16) {
+        const float s = ldexpf(1.0f, meta[k].scale_exp);
+        const float *src = embed + kc * 128 + chunk * 8;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] = __float2half_rn(src[j] * s);
+        const int kb = chunk >> 3, cidx = chunk & 7;
+        off = (size_t)kb * 16384 + (size_t)r * 128 + (size_t)((cidx ^ (r & 7)) << 4);
+    } else {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] = __float2half_rn(0.0f);
+        if (chunk == 16) {
+            const float t = -(0.5f * cnorm[kc]) * ldexpf(1.0f, meta[k].aug_exp);
+            const __half hi = __float2half_rn(t);
+            const float r1 = t - __half2float(hi);
+            const __half mid = __float2half_rn(r1);
+            const __half lo = __float2half_rn(r1 - __half2float(mid));
+            v[0] = hi; v[1] = mid; v[2] = lo;
+        }
+        off = 32768 + (size_t)(r >> 3) * 256 + (size_t)(chunk - 16) * 128 + (size_t)(r & 7) * 16;
+    }
+    *reinterpret_cast<uint4 *>(base + off) = *reinterpret_cast<const uint4 *>(v);
 }
 
 // ---------------------------------------------------------------- entry point
@@ -144,9 +167,13 @@ extern "C" int rvq_pack_codebooks(const float *const *embed_ptrs, int Ktot, int 
     rvq_cnorm_kernel<<<(unsigned)((warps * 32 + 255) / 256), 256, 0, stream>>>(
         embed, Ktot, C, D, (float *)(p + h.off_cnorm), meta);
     rvq_scale_kernel<<<1, 64, 0, stream>>>(meta, Ktot);
-    const int64_t total = per_stage * Ktot;
-    rvq_f16_kernel<<<(unsigned)((total / 4 + 255) / 256), 256, 0, stream>>>(embed, per_stage, total, meta,
-                                                                           (__half *)(p + h.off_f16));
-    rvq_count_launch(3);
+    int launches = 2;
+    if (D == 128 && C % RVQ_TC_TILE_CODES == 0) {
+        const int64_t total = (int64_t)Ktot * C * 18;
+        rvq_image_kernel<<<(unsigned)((total + 255) / 256), 256, 0, stream>>>(
+            embed, (const float *)(p + h.off_cnorm), Ktot, C, meta, (uint8_t *)(p + h.off_f16));
+        ++launches;
+    }
+    rvq_count_launch(launches);
     return rvq_check_launch("rvq_pack kernels");
 }

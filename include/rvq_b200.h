@@ -85,6 +85,17 @@ int rvq_decode_f32(const void *codes, int code_bytes, const int64_t cs[3], int B
                    const void *pack, int Ktot, int C, int D, float *out, const int64_t os[3],
                    int64_t *status, void *stream);
 
+/*
+ * Diagnostics (no counterpart in the reference): runs the tensor-core encode and also returns, for
+ * the first 128 frames and stage `stage`, the raw approximate scores of every code
+ * (acc_out, device fp32 [128][C]) and the per-frame scan state (info_out, device fp32 [128][8]:
+ * ||r||^2, alpha, 2*delta, running maximum, remembered groups, flags, score scale, augmented-column
+ * value).  Used by the tests to check the error bound that certifies the exact re-scoring.
+ */
+int rvq_debug_tc_scores(const float *x, const int64_t xs[3], int B, int D, int T, const void *pack,
+                        int Ktot, int C, int K, int stage, int64_t *codes, float *acc_out,
+                        float *info_out, void *stream);
+
 /* Introspection used by tests and the bench: number of kernels launched by this library on the
  * calling thread since the last reset (the bench's `gpu_launches`). */
 int64_t rvq_b200_launch_count(int reset);

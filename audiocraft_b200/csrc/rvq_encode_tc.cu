@@ -116,6 +116,26 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
         : "r"(taddr)
         : "memory");
 }
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+          "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+        : "r"(taddr)
+        : "memory");
+}
+__device__ __forceinline__ float max3(float a, float b, float c) {
+    float r;
+    asm("max.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c));
+    return r;
+}
+__device__ __forceinline__ float group_max8(const uint32_t *v) {
+    float m = max3(__uint_as_float(v[0]), __uint_as_float(v[1]), __uint_as_float(v[2]));
+    m = max3(m, __uint_as_float(v[3]), __uint_as_float(v[4]));
+    m = max3(m, __uint_as_float(v[5]), __uint_as_float(v[6]));
+    return fmaxf(m, __uint_as_float(v[7]));
+}
 __device__ __forceinline__ void tmem_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 // K-major SWIZZLE_128B operand: rows of 128 bytes, 8-row groups 1024 bytes apart (SBO), version 1
@@ -171,6 +191,36 @@ __device__ __forceinline__ void warp_argmax(float &bs, int &bi) {
     }
 }
 
+__device__ __forceinline__ void warp_argmax_quads(float &bs, int &bi) {
+#pragma unroll
+    for (int off = 16; off >= 4; off >>= 1) {
+        float os = __shfl_xor_sync(0xffffffffu, bs, off);
+        int oi = __shfl_xor_sync(0xffffffffu, bi, off);
+        if (rvq_better(os, oi, bs, bi)) { bs = os; bi = oi; }
+    }
+}
+
+// canonical inner products of one frame with the 8 codes of a group; lane l gets column (l >> 2) & 7
+__device__ __forceinline__ float group_dots(const float4 &rf, const float4 (&rows)[8], int lane) {
+    float p[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        float a = __fmaf_rn(rf.x, rows[j].x, 0.0f);
+        a = __fmaf_rn(rf.y, rows[j].y, a);
+        a = __fmaf_rn(rf.z, rows[j].z, a);
+        p[j] = __fmaf_rn(rf.w, rows[j].w, a);
+    }
+    return transposed_butterfly8(p, lane);
+}
+
+__device__ __forceinline__ void load_group(const float *__restrict__ Ek, const float *__restrict__ cnk, int g, int lane,
+                                           float4 (&rows)[8], float &cn) {
+    const float4 *base = reinterpret_cast<const float4 *>(Ek + (size_t)g * (8 * 128)) + lane;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) rows[j] = __ldg(base + j * 32);
+    cn = __ldg(cnk + g * 8 + ((lane >> 2) & 7));
+}
+
 // Full exact scan of one frame by one warp (lane owns dims 4*lane..4*lane+3).  Same arithmetic as
 // rvq_encode_exact.cu.  Used for frames the certified search cannot cover.
 __device__ __noinline__ int exact_scan_frame(float4 rf, float xx, const float *__restrict__ Ek,
@@ -196,9 +246,10 @@ __device__ __noinline__ int exact_scan_frame(float4 rf, float xx, const float *_
     return bidx;
 }
 
-// Exact resolution of one frame: re-score the remembered groups that can still hold the winner.
+// Exact resolution of one frame, general case (more than two surviving groups, list overflow, or a
+// frame the bound does not cover): re-score every remembered group that can still hold the winner.
 // list: this frame's entries, entry e at list[e * TILE_M]; entry = (float bits & ~0x7FF) | group.
-__device__ __noinline__ int resolve_frame(float4 rf, float xx, int cnt, float M, float twodelta, int flags,
+__device__ __noinline__ int resolve_slow(float4 rf, float xx, int cnt, float M, float twodelta, int flags,
                                           const uint32_t *list, const float *__restrict__ Ek,
                                           const float *__restrict__ cnk, int C, int lane) {
     int idx;
@@ -235,6 +286,46 @@ __device__ __noinline__ int resolve_frame(float4 rf, float xx, int cnt, float M,
     return idx;
 }
 
+// Per-frame power-of-two scaling of the fp16 residual operand.
+struct FrameScale {
+    int flags;  // 0: covered by the certified search; else the frame takes the exact scan
+    int ea;     // operand = residual * 2^ea, so that 2^ea * ||r|| lies in (0.35, 1]
+};
+__device__ __forceinline__ FrameScale frame_scale(float xx, const RvqStageMeta &mt) {
+    FrameScale fs;
+    fs.flags = mt.flags ? 4 : 0;
+    fs.ea = 0;
+    if (!(xx <= 3.0e38f)) fs.flags |= 1;  // NaN or Inf
+    if (xx > 0.0f && fs.flags == 0) {
+        int e2;
+        frexpf(xx, &e2);           // xx = m * 2^e2, m in [0.5, 1)  ->  ||r|| <= 2^ceil(e2/2)
+        fs.ea = -((e2 + 1) >> 1);
+    }
+    const int aexp = fs.ea + mt.scale_exp - mt.aug_exp;  // exponent of the augmented operand column
+    if (aexp < -24 || aexp > 15) fs.flags |= 2;
+    return fs;
+}
+
+// ||r||^2 (canonical order, every lane gets it) of the frame whose 4 dims per lane are `rf`, and its fp16
+// operand row `row` of the SWIZZLE_128B image A (rvq_common.cuh) for the stage described by `mt`.
+__device__ __forceinline__ float emit_row(uint8_t *A, int row, int lane, const float4 &rf, const RvqStageMeta &mt) {
+    float a = __fmaf_rn(rf.x, rf.x, 0.0f);
+    a = __fmaf_rn(rf.y, rf.y, a);
+    a = __fmaf_rn(rf.z, rf.z, a);
+    a = __fmaf_rn(rf.w, rf.w, a);
+    const float xx = rvq_butterfly(a);
+    const FrameScale fs = frame_scale(xx, mt);
+    const float al = fs.flags ? 0.0f : ldexpf(1.0f, fs.ea);
+    const __half2 h0 = __floats2half2_rn(rf.x * al, rf.y * al);
+    const __half2 h1 = __floats2half2_rn(rf.z * al, rf.w * al);
+    const int off = (lane >> 4) * 16384 + row * 128 + ((((lane & 15) >> 1) ^ (row & 7)) << 4) + (lane & 1) * 8;
+    uint2 w;
+    w.x = *reinterpret_cast<const uint32_t *>(&h0);
+    w.y = *reinterpret_cast<const uint32_t *>(&h1);
+    *reinterpret_cast<uint2 *>(A + off) = w;
+    return xx;
+}
+
 struct TcParams {
     const float *x;
     int64_t xs_b, xs_d, xs_t;
@@ -247,6 +338,7 @@ struct TcParams {
     const RvqStageMeta *meta;
     int C, K, NT;         // NT = C / 128
     int64_t *codes;       // [K][N]
+    float *scratch;       // residuals of the tiles in flight: [grid][2 slots][128 frames][128] fp32
     // diagnostics (optional): accumulators and per-frame scan state of CTA 0 / slot 0 / first tile
     float *dbg_acc;       // [128][C] raw accumulators of stage dbg_stage
     float *dbg_info;      // [128][8]
@@ -261,6 +353,7 @@ __device__ __forceinline__ int slot_tiles(int ntiles, int grid, int cta, int slo
 }
 
 // ------------------------------------------------------------------------------------ kernel
+template <bool DBG>
 __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParams P) {
     extern __shared__ uint8_t smem_raw[];
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -359,99 +452,62 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
         uint32_t *list = reinterpret_cast<uint32_t *>(sm + SM_LIST) + slot * LISTCAP * TILE_M;
         const int row_l = q * 32 + lane;  // the row (frame of the tile) this thread scans
         const int C = P.C;
+        // this warp's 32 residual rows [frame][128] fp32 in the L2-resident scratch
+        float *rs = P.scratch + ((size_t)(cta * NSLOT + slot) * TILE_M + q * 32) * 128;
+        float4 *rs4 = reinterpret_cast<float4 *>(rs) + lane;  // + f * 32: this lane's 4 dims of frame f
         uint32_t items = 0;  // accumulator uses of this slot so far
+        const bool direct = P.xs_d == 1 && (P.xs_b & 3) == 0 && (P.xs_t & 3) == 0 && ((uintptr_t)P.x & 15) == 0;
 
         for (int tile = cta + grid * slot, first = 1; tile < P.ntiles; tile += 2 * grid, first = 0) {
             const int64_t n0 = (int64_t)tile * TILE_M + q * 32;
-            // ---- residual: lane owns dims 4*lane..4*lane+3 of each of the warp's 32 frames
-            float4 r[32];
-            if (P.xs_d == 1 && (P.xs_b & 3) == 0 && (P.xs_t & 3) == 0 && ((uintptr_t)P.x & 15) == 0) {
-#pragma unroll
-                for (int f = 0; f < 32; ++f) {
-                    const int64_t n = n0 + f;
-                    r[f] = make_float4(0.f, 0.f, 0.f, 0.f);
-                    if (n < P.N)
-                        r[f] = *reinterpret_cast<const float4 *>(P.x + (n / P.T) * P.xs_b + (n % P.T) * P.xs_t + 4 * lane);
-                }
-            } else {
-                // lane = frame reads (coalesced when T is the contiguous axis), transposed through this
-                // warp's own 4 KB of the A tile, 32 dims at a time
-                const int64_t n = n0 + lane;
-                const bool valid = n < P.N;
-                const float *xp = P.x + (valid ? (n / P.T) * P.xs_b + (n % P.T) * P.xs_t : 0);
+            // lane = frame: where this lane's frame starts in x (-1: past the end)
+            const int64_t n_l = n0 + lane;
+            const int64_t xoff = n_l < P.N ? (n_l / P.T) * P.xs_b + (n_l % P.T) * P.xs_t : -1;
+            if (!direct) {
+                // lane = frame reads (coalesced when T is the contiguous axis), transposed 32 dims at a
+                // time through this warp's own 4 KB of the A tile into the scratch rows
                 float *st = reinterpret_cast<float *>(A + q * 4096);
-#pragma unroll
                 for (int pass = 0; pass < 4; ++pass) {
                     __syncwarp();
 #pragma unroll 8
                     for (int dd = 0; dd < 32; ++dd)
-                        st[dd * 32 + (lane ^ dd)] = valid ? xp[(int64_t)(pass * 32 + dd) * P.xs_d] : 0.0f;
+                        st[dd * 32 + (lane ^ dd)] = xoff >= 0 ? P.x[xoff + (int64_t)(pass * 32 + dd) * P.xs_d] : 0.0f;
                     __syncwarp();
-                    if ((lane >> 3) == pass) {
-                        const int dl = 4 * (lane & 7);
-#pragma unroll
-                        for (int f = 0; f < 32; ++f) {
-                            r[f].x = st[(dl + 0) * 32 + (f ^ (dl + 0))];
-                            r[f].y = st[(dl + 1) * 32 + (f ^ (dl + 1))];
-                            r[f].z = st[(dl + 2) * 32 + (f ^ (dl + 2))];
-                            r[f].w = st[(dl + 3) * 32 + (f ^ (dl + 3))];
-                        }
-                    }
+#pragma unroll 8
+                    for (int f = 0; f < 32; ++f) rs[f * 128 + pass * 32 + lane] = st[lane * 32 + (f ^ lane)];
                 }
                 __syncwarp();
+            }
+
+            // ---- stage 0 operand rows; lane f keeps ||r_f||^2
+            RvqStageMeta mt = P.meta[0];
+            float xx = 0.0f;
+            for (int f = 0; f < 32; ++f) {
+                float4 rf;
+                if (direct) {
+                    const int64_t o = __shfl_sync(0xffffffffu, xoff, f);
+                    rf = o >= 0 ? *(reinterpret_cast<const float4 *>(P.x + o) + lane) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    rs4[f * 32] = rf;
+                } else {
+                    rf = rs4[f * 32];
+                }
+                const float xv = emit_row(A, q * 32 + f, lane, rf, mt);
+                if (lane == f) xx = xv;
             }
 
             for (int k = 0; k < K; ++k) {
                 const float *Ek = P.embed + (size_t)k * C * 128;
                 const float *cnk = P.cnorm + (size_t)k * C;
-                const RvqStageMeta mt = P.meta[k];
-                // ---- ||r||^2 of the 32 frames in canonical order; lane f ends up with frame f's
-                float xx;
-                {
-                    float p[32];
-#pragma unroll
-                    for (int f = 0; f < 32; ++f) {
-                        float a = __fmaf_rn(r[f].x, r[f].x, 0.0f);
-                        a = __fmaf_rn(r[f].y, r[f].y, a);
-                        a = __fmaf_rn(r[f].z, r[f].z, a);
-                        p[f] = __fmaf_rn(r[f].w, r[f].w, a);
-                    }
-                    transposed_butterfly32(p, lane);
-                    xx = p[0];
-                }
-                // ---- per-frame scaling and error bound (this thread's frame = lane)
-                int flags = mt.flags ? 4 : 0;
-                int ea = 0;
-                if (!(xx <= 3.0e38f)) flags |= 1;  // NaN or Inf
-                if (xx > 0.0f && flags == 0) {
-                    int e2;
-                    frexpf(xx, &e2);        // xx = m * 2^e2, m in [0.5, 1)  ->  ||r|| <= 2^ceil(e2/2)
-                    ea = -((e2 + 1) >> 1);  // alpha * ||r|| in (0.35, 1]
-                }
-                const int aexp = ea + mt.scale_exp - mt.aug_exp;
-                if (aexp < -24 || aexp > 15) flags |= 2;
-                const float alpha = flags ? 0.0f : ldexpf(1.0f, ea);
-                const float scale_acc = ldexpf(1.0f, ea + mt.scale_exp);  // acc ~= scale_acc * (r.c - cc/2)
+                // ---- this thread's frame (= lane): error bound, augmented operand column, hand-over
+                const FrameScale fs = frame_scale(xx, mt);
+                const int flags = fs.flags;
+                const float scale_acc = ldexpf(1.0f, fs.ea + mt.scale_exp);  // acc ~= scale_acc * (r.c - cc/2)
                 const float R = sqrtf(xx), cn_max = sqrtf(mt.cnorm2_max);
-                const float e16 = 0.0009765625f * scale_acc * R * cn_max;          // 2^-10: fp16 rounding of both operands
+                const float e16 = 0.0009765625f * scale_acc * R * cn_max;  // 2^-10: fp16 rounding of both operands
                 const float e32 = 2.384185791015625e-07f * (xx + 2.0f * R * cn_max + mt.cnorm2_max) +
-                                  3.814697265625e-06f * R * cn_max;                 // canonical fp32 evaluation
+                                  3.814697265625e-06f * R * cn_max;         // canonical fp32 evaluation
                 const float twodelta = 2.0002f * (1.2505f * e16 + 0.5f * scale_acc * e32 + 1.0f);
-                const __half a_aug = __float2half_rn(flags ? 0.0f : ldexpf(1.0f, aexp));
-
-                // ---- fp16 operand rows of this warp's frames (SWIZZLE_128B image, see rvq_common.cuh)
-#pragma unroll
-                for (int f = 0; f < 32; ++f) {
-                    const float al = __shfl_sync(0xffffffffu, alpha, f);
-                    const __half2 h0 = __floats2half2_rn(r[f].x * al, r[f].y * al);
-                    const __half2 h1 = __floats2half2_rn(r[f].z * al, r[f].w * al);
-                    const int row = q * 32 + f;
-                    const int off = (lane >> 4) * 16384 + row * 128 + ((((lane & 15) >> 1) ^ (f & 7)) << 4) + (lane & 1) * 8;
-                    uint2 w;
-                    w.x = *reinterpret_cast<const uint32_t *>(&h0);
-                    w.y = *reinterpret_cast<const uint32_t *>(&h1);
-                    *reinterpret_cast<uint2 *>(A + off) = w;
-                }
+                const __half a_aug = __float2half_rn(flags ? 0.0f : ldexpf(1.0f, fs.ea + mt.scale_exp - mt.aug_exp));
                 {
                     const uint32_t h = (uint32_t)__half_as_ushort(a_aug);
                     uint8_t *ar = A + 32768 + (row_l >> 3) * 256 + (row_l & 7) * 16;
@@ -465,31 +521,31 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
                 // ---- scan: this thread's frame = TMEM lane row_l
                 float M = -CUDART_INF_F, thr = -CUDART_INF_F;
                 int cnt = 0;
-                const bool dbg = P.dbg_acc != nullptr && cta == 0 && slot == 0 && first && k == P.dbg_stage;
+                const bool dbg = DBG && cta == 0 && slot == 0 && first && k == P.dbg_stage;
                 for (int j = 0; j < NT; ++j, ++items) {
                     const int buf = items & 1;
                     mbar_wait(BAR(BAR_ACCFULL + slot * 2 + buf), (items >> 1) & 1u);
                     tc_fence_after();
                     const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(slot * 256 + buf * 128);
-#pragma unroll 1
-                    for (int ch = 0; ch < 4; ++ch) {
-                        uint32_t v[32];
-                        tmem_ld32(taddr + ch * 32, v);
-                        tmem_wait_ld();
-                        if (dbg) {
+                    // 8 chunks of 16 columns, the load of chunk c+1 in flight while chunk c is reduced
+                    uint32_t va[16], vb[16];
+                    tmem_ld16(taddr, va);
 #pragma unroll
-                            for (int i = 0; i < 32; ++i)
-                                P.dbg_acc[(size_t)row_l * C + j * 128 + ch * 32 + i] = __uint_as_float(v[i]);
+                    for (int ch = 0; ch < 8; ++ch) {
+                        uint32_t(&v)[16] = (ch & 1) ? vb : va;
+                        tmem_wait_ld();
+                        if (ch + 1 < 8) tmem_ld16(taddr + (ch + 1) * 16, (ch & 1) ? va : vb);
+                        if (DBG && dbg) {
+#pragma unroll
+                            for (int i = 0; i < 16; ++i)
+                                P.dbg_acc[(size_t)row_l * C + j * 128 + ch * 16 + i] = __uint_as_float(v[i]);
                         }
 #pragma unroll
-                        for (int g = 0; g < 4; ++g) {
-                            float gm = fmaxf(fmaxf(__uint_as_float(v[8 * g]), __uint_as_float(v[8 * g + 1])),
-                                             fmaxf(__uint_as_float(v[8 * g + 2]), __uint_as_float(v[8 * g + 3])));
-                            gm = fmaxf(gm, fmaxf(fmaxf(__uint_as_float(v[8 * g + 4]), __uint_as_float(v[8 * g + 5])),
-                                                 fmaxf(__uint_as_float(v[8 * g + 6]), __uint_as_float(v[8 * g + 7]))));
+                        for (int g = 0; g < 2; ++g) {
+                            const float gm = group_max8(&v[8 * g]);
                             if (gm >= thr) {
                                 if (cnt < LISTCAP)
-                                    list[cnt * TILE_M + row_l] = (__float_as_uint(gm) & ~0x7FFu) | (uint32_t)(j * 16 + ch * 4 + g);
+                                    list[cnt * TILE_M + row_l] = (__float_as_uint(gm) & ~0x7FFu) | (uint32_t)(j * 16 + ch * 2 + g);
                                 ++cnt;
                             }
                             M = fmaxf(M, gm);
@@ -500,32 +556,83 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
                     __syncwarp();
                     if (lane == 0) mbar_arrive(BAR(BAR_ACCEMPTY + slot * 2 + buf));
                 }
-                if (dbg) {
+                if (DBG && dbg) {
                     float *o = P.dbg_info + row_l * 8;
-                    o[0] = xx; o[1] = alpha; o[2] = twodelta; o[3] = M; o[4] = (float)cnt; o[5] = (float)flags;
-                    o[6] = scale_acc; o[7] = __half2float(a_aug);
+                    o[0] = xx; o[1] = flags ? 0.0f : ldexpf(1.0f, fs.ea); o[2] = twodelta; o[3] = M; o[4] = (float)cnt;
+                    o[5] = (float)flags; o[6] = scale_acc; o[7] = __half2float(a_aug);
                 }
-                __syncwarp();  // the lists written by lane = frame are read by every lane below
 
-                // ---- resolve, frame by frame (warp cooperative), then the coalesced code store
+                // ---- resolve, phase 1 (lane = frame): which remembered groups can still hold the winner?
+                // nh = 1: only group h0 (the common case); anything else goes to resolve_slow
+                int nh = 99;
+                uint32_t h0 = 0;
+                if (flags == 0 && cnt <= LISTCAP) {
+                    // entries were stored with 11 mantissa bits cleared: allow for that when filtering
+                    const float keep = M - twodelta - 0.0009765625f * (fabsf(M) + twodelta);
+                    nh = 0;
+                    for (int e = 0; e < cnt; ++e) {
+                        const uint32_t u = list[e * TILE_M + row_l];
+                        if (__uint_as_float(u & ~0x7FFu) >= keep) {
+                            if (nh == 0) h0 = u & 0x7FFu;
+                            ++nh;
+                        }
+                    }
+                }
+                __syncwarp();  // lists (written by lane = frame) are read by every lane in resolve_slow
+
+                // ---- resolve, phase 2: frame by frame, warp cooperative, exact fp32 in the canonical order,
+                // fused with the residual update and the next stage's operand row.  The rows of frame
+                // f+1's group and its residual are requested before frame f is reduced.
+                const bool more = k + 1 < K;
+                if (more) mt = P.meta[k + 1];
                 int mycode = 0;
-#pragma unroll
+                float xx_next = 0.0f;
+                float4 rows[8], rf = rs4[0];
+                float cn0;
+                int g_cur = __shfl_sync(0xffffffffu, (int)h0, 0);
+                load_group(Ek, cnk, g_cur, lane, rows, cn0);
+#pragma unroll 1
                 for (int f = 0; f < 32; ++f) {
+                    const int fn = min(f + 1, 31);
+                    float4 rows_n[8], rf_n = rs4[fn * 32];
+                    float cn_n;
+                    const int g_next = __shfl_sync(0xffffffffu, (int)h0, fn);
+                    load_group(Ek, cnk, g_next, lane, rows_n, cn_n);
                     const float xf = __shfl_sync(0xffffffffu, xx, f);
-                    const int cf = __shfl_sync(0xffffffffu, cnt, f);
-                    const float Mf = __shfl_sync(0xffffffffu, M, f);
-                    const float tf = __shfl_sync(0xffffffffu, twodelta, f);
-                    const int ff = __shfl_sync(0xffffffffu, flags, f);
-                    const int idx = resolve_frame(r[f], xf, cf, Mf, tf, ff, list + q * 32 + f, Ek, cnk, C, lane);
+                    const int nf = __shfl_sync(0xffffffffu, nh, f);
+                    int idx;
+                    if (nf == 1) {  // warp uniform
+                        float bs = rvq_score(xf, group_dots(rf, rows, lane), cn0);
+                        int bi = g_cur * 8 + ((lane >> 2) & 7);
+                        warp_argmax_quads(bs, bi);
+                        idx = bi;
+                    } else {
+                        const int cf = __shfl_sync(0xffffffffu, cnt, f);
+                        const float Mf = __shfl_sync(0xffffffffu, M, f);
+                        const float tf = __shfl_sync(0xffffffffu, twodelta, f);
+                        const int ff = __shfl_sync(0xffffffffu, flags, f);
+                        idx = resolve_slow(rf, xf, cf, Mf, tf, ff, list + q * 32 + f, Ek, cnk, C, lane);
+                    }
                     if (lane == f) mycode = idx;
-                    // residual = residual - quantized (core_vq.py:394)
-                    const float4 w = __ldg(reinterpret_cast<const float4 *>(Ek + (size_t)idx * 128) + lane);
-                    r[f].x = __fsub_rn(r[f].x, w.x);
-                    r[f].y = __fsub_rn(r[f].y, w.y);
-                    r[f].z = __fsub_rn(r[f].z, w.z);
-                    r[f].w = __fsub_rn(r[f].w, w.w);
+                    if (more) {
+                        // residual = residual - quantized (core_vq.py:394)
+                        const float4 w = __ldg(reinterpret_cast<const float4 *>(Ek + (size_t)idx * 128) + lane);
+                        rf.x = __fsub_rn(rf.x, w.x);
+                        rf.y = __fsub_rn(rf.y, w.y);
+                        rf.z = __fsub_rn(rf.z, w.z);
+                        rf.w = __fsub_rn(rf.w, w.w);
+                        rs4[f * 32] = rf;
+                        const float xv = emit_row(A, q * 32 + f, lane, rf, mt);
+                        if (lane == f) xx_next = xv;
+                    }
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) rows[j] = rows_n[j];
+                    cn0 = cn_n;
+                    g_cur = g_next;
+                    rf = rf_n;
                 }
                 if (n0 + lane < P.N) P.codes[(int64_t)k * P.N + n0 + lane] = (int64_t)mycode;
+                xx = xx_next;
                 __syncwarp();
             }
         }
@@ -543,16 +650,37 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
 // ------------------------------------------------------------------------------------ host
 bool rvq_tc_shape_supported(int D, int C) { return D == 128 && C % 128 == 0 && C >= 256 && C <= 16384; }
 
+static int device_sms(int *sms) {
+    int dev = 0;
+    RVQ_CUDA(cudaGetDevice(&dev));
+    RVQ_CUDA(cudaDeviceGetAttribute(sms, cudaDevAttrMultiProcessorCount, dev));
+    return RVQ_OK;
+}
+
+static int tc_grid(int64_t N, int sms) {
+    const int64_t ntiles = (N + TILE_M - 1) / TILE_M;
+    int64_t grid = (ntiles + NSLOT - 1) / NSLOT;
+    if (grid > sms) grid = sms;
+    return (int)(grid < 1 ? 1 : grid);
+}
+
+// workspace = [256 B: decode status word] [grid x 2 slots x 128 frames x 128 fp32: residual scratch]
+constexpr int64_t WS_HEADER = 256;
+constexpr int64_t WS_PER_CTA = (int64_t)NSLOT * TILE_M * 128 * 4;
+
 int64_t rvq_tc_workspace_bytes(int B, int D, int T, int K, int C) {
-    (void)B; (void)D; (void)T; (void)K; (void)C;
-    return 256;  // the decode status word used when the quantized output is requested
+    (void)D; (void)K; (void)C;
+    int sms = 0;
+    if (device_sms(&sms) != RVQ_OK) return RVQ_ECUDA;
+    return WS_HEADER + WS_PER_CTA * tc_grid((int64_t)B * T, sms);
 }
 
 int rvq_decode_launch_internal(const int64_t *codes_kbt, int B, int K, int T, const RvqPackView &pv, float *out,
                                int64_t *status, cudaStream_t stream);
 
 static int launch_tc(const float *x, const int64_t xs[3], int B, int T, const RvqPackView &pv, int K, int64_t *codes,
-                     float *dbg_acc, float *dbg_info, int dbg_stage, cudaStream_t stream) {
+                     void *workspace, int64_t workspace_bytes, float *dbg_acc, float *dbg_info, int dbg_stage,
+                     cudaStream_t stream) {
     TcParams P;
     P.x = x; P.xs_b = xs[0]; P.xs_d = xs[1]; P.xs_t = xs[2];
     P.B = B; P.T = T; P.N = (int64_t)B * T;
@@ -562,17 +690,20 @@ static int launch_tc(const float *x, const int64_t xs[3], int B, int T, const Rv
     P.C = pv.C; P.K = K; P.NT = pv.C / 128;
     P.codes = codes;
     P.dbg_acc = dbg_acc; P.dbg_info = dbg_info; P.dbg_stage = dbg_stage;
-    int dev = 0, sms = 148;
-    RVQ_CUDA(cudaGetDevice(&dev));
-    RVQ_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    int grid = (P.ntiles + NSLOT - 1) / NSLOT;
-    if (grid > sms) grid = sms;
-    static bool attr_set[64] = {false};
-    if (dev < 64 && !attr_set[dev]) {
-        RVQ_CUDA(cudaFuncSetAttribute(rvq_encode_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_ALLOC));
-        attr_set[dev] = true;
+    int sms = 0;
+    int rc = device_sms(&sms);
+    if (rc != RVQ_OK) return rc;
+    const int grid = tc_grid(P.N, sms);
+    RVQ_REQUIRE(workspace && workspace_bytes >= WS_HEADER + WS_PER_CTA * grid && ((uintptr_t)workspace & 15) == 0,
+                RVQ_EINVAL, "rvq_encode_f32: a 16-byte aligned workspace of rvq_encode_workspace_bytes() bytes is required");
+    P.scratch = reinterpret_cast<float *>((char *)workspace + WS_HEADER);
+    if (dbg_acc) {
+        RVQ_CUDA(cudaFuncSetAttribute(rvq_encode_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_ALLOC));
+        rvq_encode_tc_kernel<true><<<grid, THREADS, SM_ALLOC, stream>>>(P);
+    } else {
+        RVQ_CUDA(cudaFuncSetAttribute(rvq_encode_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_ALLOC));
+        rvq_encode_tc_kernel<false><<<grid, THREADS, SM_ALLOC, stream>>>(P);
     }
-    rvq_encode_tc_kernel<<<grid, THREADS, SM_ALLOC, stream>>>(P);
     rvq_count_launch(1);
     return rvq_check_launch("rvq_encode_tc_kernel");
 }
@@ -581,9 +712,7 @@ int rvq_encode_tc(const float *x, const int64_t xs[3], int B, int D, int T, cons
                   int K, int64_t *codes, float *quantized, void *workspace, int64_t workspace_bytes,
                   cudaStream_t stream) {
     (void)pack; (void)D;
-    RVQ_REQUIRE(!quantized || (workspace && workspace_bytes >= 16), RVQ_EINVAL,
-                "rvq_encode_f32: workspace of rvq_encode_workspace_bytes() bytes required");
-    int rc = launch_tc(x, xs, B, T, pv, K, codes, nullptr, nullptr, 0, stream);
+    int rc = launch_tc(x, xs, B, T, pv, K, codes, workspace, workspace_bytes, nullptr, nullptr, 0, stream);
     if (rc != RVQ_OK || !quantized) return rc;
     // quantized_out = 0 + q_0 + ... (core_vq.py:363-385): the gather-sum kernel on the codes just written
     RVQ_CUDA(cudaMemsetAsync(workspace, 0, 16, stream));
@@ -593,10 +722,11 @@ int rvq_encode_tc(const float *x, const int64_t xs[3], int B, int D, int T, cons
 // Diagnostics: raw tensor-core accumulators and scan state of the first 128 frames, stage `stage`.
 extern "C" int rvq_debug_tc_scores(const float *x, const int64_t xs[3], int B, int D, int T, const void *pack, int Ktot,
                                    int C, int K, int stage, int64_t *codes, float *acc_out, float *info_out,
-                                   void *stream_) {
+                                   void *workspace, int64_t workspace_bytes, void *stream_) {
     RVQ_REQUIRE(x && xs && pack && codes && acc_out && info_out, RVQ_EINVAL, "rvq_debug_tc_scores: null pointer");
     RVQ_REQUIRE(rvq_tc_shape_supported(D, C) && K > 0 && K <= Ktot && stage >= 0 && stage < K, RVQ_EUNSUPPORTED,
                 "rvq_debug_tc_scores: shape not covered by the tensor-core path");
     RvqPackView pv = rvq_pack_view(pack, Ktot, C, D);
-    return launch_tc(x, xs, B, T, pv, K, codes, acc_out, info_out, stage, (cudaStream_t)stream_);
+    return launch_tc(x, xs, B, T, pv, K, codes, workspace, workspace_bytes, acc_out, info_out, stage,
+                     (cudaStream_t)stream_);
 }

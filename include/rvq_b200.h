@@ -63,7 +63,10 @@ int rvq_pack_codebooks(const float *const *embed_ptrs, int Ktot, int C, int D, v
  *              the caller returns codes.transpose(0,1) like vq.py:94
  *   quantized  NULL, or device fp32 [B][T][D] contiguous receiving 0.0f + q_0 + ... + q_{K-1}
  *              (eval ResidualVectorQuantization.forward, core_vq.py:363-385)
- *   workspace  device scratch of rvq_encode_workspace_bytes() bytes (may be NULL when that is 0)
+ *   workspace  device scratch of rvq_encode_workspace_bytes() bytes, 16-byte aligned (may be NULL when
+ *              that is 0).  The tensor-core path keeps the residuals of the frame tiles in flight there
+ *              (128 KB per resident CTA, L2 resident); contents need not be preserved between calls,
+ *              but two encodes that overlap on the GPU must not share it
  */
 int64_t rvq_encode_workspace_bytes(int B, int D, int T, int K, int C, int algo);
 int rvq_encode_f32(const float *x, const int64_t xs[3], int B, int D, int T, const void *pack,
@@ -91,10 +94,11 @@ int rvq_decode_f32(const void *codes, int code_bytes, const int64_t cs[3], int B
  * (acc_out, device fp32 [128][C]) and the per-frame scan state (info_out, device fp32 [128][8]:
  * ||r||^2, alpha, 2*delta, running maximum, remembered groups, flags, score scale, augmented-column
  * value).  Used by the tests to check the error bound that certifies the exact re-scoring.
+ * workspace: as for rvq_encode_f32 with RVQ_ALGO_TC.
  */
 int rvq_debug_tc_scores(const float *x, const int64_t xs[3], int B, int D, int T, const void *pack,
                         int Ktot, int C, int K, int stage, int64_t *codes, float *acc_out,
-                        float *info_out, void *stream);
+                        float *info_out, void *workspace, int64_t workspace_bytes, void *stream);
 
 /* Introspection used by tests and the bench: number of kernels launched by this library on the
  * calling thread since the last reset (the bench's `gpu_launches`). */

@@ -23,8 +23,10 @@ def tc_scores(m, x, stage):
     codes = torch.empty((K, B, T), dtype=torch.int64, device=x.device)
     acc = torch.full((128, C), float("nan"), device=x.device)
     info = torch.zeros((128, 8), device=x.device)
+    ws_bytes = lib.rvq_encode_workspace_bytes(B, D, T, K, C, _lib.ALGO_TC)
+    ws = torch.empty(ws_bytes, dtype=torch.uint8, device=x.device)
     rc = lib.rvq_debug_tc_scores(x.data_ptr(), _lib.strides3(x.stride()), B, D, T, pack.data_ptr(), Ktot, C, K,
-                                 stage, codes.data_ptr(), acc.data_ptr(), info.data_ptr(),
+                                 stage, codes.data_ptr(), acc.data_ptr(), info.data_ptr(), ws.data_ptr(), ws_bytes,
                                  torch.cuda.current_stream().cuda_stream)
     _lib.check(rc, "rvq_debug_tc_scores")
     torch.cuda.synchronize()

@@ -104,18 +104,6 @@ __device__ __forceinline__ void umma_f16(uint32_t d_tmem, uint64_t adesc, uint64
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
-__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
-    asm volatile(
-        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
-        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
-          "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),
-          "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
-          "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
-        : "r"(taddr)
-        : "memory");
-}
 __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
     asm volatile(
         "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
@@ -191,15 +179,6 @@ __device__ __forceinline__ void warp_argmax(float &bs, int &bi) {
     }
 }
 
-__device__ __forceinline__ void warp_argmax_quads(float &bs, int &bi) {
-#pragma unroll
-    for (int off = 16; off >= 4; off >>= 1) {
-        float os = __shfl_xor_sync(0xffffffffu, bs, off);
-        int oi = __shfl_xor_sync(0xffffffffu, bi, off);
-        if (rvq_better(os, oi, bs, bi)) { bs = os; bi = oi; }
-    }
-}
-
 // canonical inner products of one frame with the 8 codes of a group; lane l gets column (l >> 2) & 7
 __device__ __forceinline__ float group_dots(const float4 &rf, const float4 (&rows)[8], int lane) {
     float p[8];
@@ -211,14 +190,6 @@ __device__ __forceinline__ float group_dots(const float4 &rf, const float4 (&row
         p[j] = __fmaf_rn(rf.w, rows[j].w, a);
     }
     return transposed_butterfly8(p, lane);
-}
-
-__device__ __forceinline__ void load_group(const float *__restrict__ Ek, const float *__restrict__ cnk, int g, int lane,
-                                           float4 (&rows)[8], float &cn) {
-    const float4 *base = reinterpret_cast<const float4 *>(Ek + (size_t)g * (8 * 128)) + lane;
-#pragma unroll
-    for (int j = 0; j < 8; ++j) rows[j] = __ldg(base + j * 32);
-    cn = __ldg(cnk + g * 8 + ((lane >> 2) & 7));
 }
 
 // Full exact scan of one frame by one warp (lane owns dims 4*lane..4*lane+3).  Same arithmetic as
@@ -246,45 +217,51 @@ __device__ __noinline__ int exact_scan_frame(float4 rf, float xx, const float *_
     return bidx;
 }
 
-// Exact resolution of one frame, general case (more than two surviving groups, list overflow, or a
-// frame the bound does not cover): re-score every remembered group that can still hold the winner.
+// Exact resolution of one frame, general case (many candidate codes, list overflow, or a frame the
+// bound does not cover): re-score every remembered group (16 codes) that can still hold the winner.
 // list: this frame's entries, entry e at list[e * TILE_M]; entry = (float bits & ~0x7FF) | group.
 __device__ __noinline__ int resolve_slow(float4 rf, float xx, int cnt, float M, float twodelta, int flags,
                                           const uint32_t *list, const float *__restrict__ Ek,
                                           const float *__restrict__ cnk, int C, int lane) {
-    int idx;
-    if (flags != 0 || cnt > LISTCAP) {
-        idx = exact_scan_frame(rf, xx, Ek, cnk, C, lane);
-    } else {
-        // entries were stored with 11 mantissa bits cleared: allow for that when filtering
-        const float thr = M - twodelta - 0.0009765625f * (fabsf(M) + twodelta);
-        float best = -CUDART_INF_F;
-        int bidx = INT_MAX;
-        for (int e = 0; e < cnt; ++e) {
-            const uint32_t u = list[e * TILE_M];
-            const float val = __uint_as_float(u & ~0x7FFu);
-            if (!(val >= thr)) continue;  // warp uniform
-            const int c0 = (int)(u & 0x7FFu) * 8;
-            float p[8];
+    if (flags != 0 || cnt > LISTCAP) return exact_scan_frame(rf, xx, Ek, cnk, C, lane);
+    // entries were stored with 11 mantissa bits cleared: allow for that when filtering
+    const float thr = M - twodelta - 0.0009765625f * (fabsf(M) + twodelta);
+    float best = -CUDART_INF_F;
+    int bidx = INT_MAX;
+    for (int e = 0; e < cnt; ++e) {
+        const uint32_t u = list[e * TILE_M];
+        const float val = __uint_as_float(u & ~0x7FFu);
+        if (!(val >= thr)) continue;  // warp uniform
+#pragma unroll 1
+        for (int half = 0; half < 2; ++half) {
+            const int c0 = (int)(u & 0x7FFu) * 16 + half * 8;
+            float4 rows[8];
+            const float4 *base = reinterpret_cast<const float4 *>(Ek + (size_t)c0 * 128) + lane;
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                const float4 ev = __ldg(reinterpret_cast<const float4 *>(Ek + (size_t)(c0 + j) * 128) + lane);
-                float a = __fmaf_rn(rf.x, ev.x, 0.0f);
-                a = __fmaf_rn(rf.y, ev.y, a);
-                a = __fmaf_rn(rf.z, ev.z, a);
-                p[j] = __fmaf_rn(rf.w, ev.w, a);
-            }
-            const float dot = transposed_butterfly8(p, lane);
+            for (int j = 0; j < 8; ++j) rows[j] = __ldg(base + j * 32);
+            const float dot = group_dots(rf, rows, lane);
             const int col = c0 + ((lane >> 2) & 7);
             const float s = rvq_score(xx, dot, cnk[col]);
             if (rvq_better(s, col, best, bidx)) { best = s; bidx = col; }
         }
-        warp_argmax(best, bidx);
-        idx = bidx;
-        if (idx == INT_MAX) idx = exact_scan_frame(rf, xx, Ek, cnk, C, lane);  // cannot happen; stay total
     }
-    return idx;
+    warp_argmax(best, bidx);
+    if (bidx == INT_MAX) bidx = exact_scan_frame(rf, xx, Ek, cnk, C, lane);  // cannot happen; stay total
+    return bidx;
 }
+
+// canonical score of one code for one frame (warp cooperative; every lane gets the same bits)
+__device__ __forceinline__ float exact_score(const float4 &rf, float xx, const float *__restrict__ Ek,
+                                             const float *__restrict__ cnk, int col, int lane) {
+    const float4 e = __ldg(reinterpret_cast<const float4 *>(Ek + (size_t)col * 128) + lane);
+    float a = __fmaf_rn(rf.x, e.x, 0.0f);
+    a = __fmaf_rn(rf.y, e.y, a);
+    a = __fmaf_rn(rf.z, e.z, a);
+    a = __fmaf_rn(rf.w, e.w, a);
+    return rvq_score(xx, rvq_butterfly(a), __ldg(cnk + col));
+}
+
+__device__ __forceinline__ float exp2i(int e) { return __uint_as_float((uint32_t)(127 + e) << 23); }  // 2^e, |e| <= 126
 
 // Per-frame power-of-two scaling of the fp16 residual operand.
 struct FrameScale {
@@ -296,10 +273,14 @@ __device__ __forceinline__ FrameScale frame_scale(float xx, const RvqStageMeta &
     fs.flags = mt.flags ? 4 : 0;
     fs.ea = 0;
     if (!(xx <= 3.0e38f)) fs.flags |= 1;  // NaN or Inf
-    if (xx > 0.0f && fs.flags == 0) {
-        int e2;
-        frexpf(xx, &e2);           // xx = m * 2^e2, m in [0.5, 1)  ->  ||r|| <= 2^ceil(e2/2)
+    const uint32_t b = __float_as_uint(xx);
+    const int E = (int)(b >> 23);         // biased exponent (xx >= 0)
+    if (E != 0) {
+        // xx = m * 2^e2 with m in [0.5, 1)  ->  ||r|| <= 2^ceil(e2/2)
+        const int e2 = E - 126;
         fs.ea = -((e2 + 1) >> 1);
+    } else if (b != 0) {
+        fs.flags |= 2;  // subnormal ||r||^2
     }
     const int aexp = fs.ea + mt.scale_exp - mt.aug_exp;  // exponent of the augmented operand column
     if (aexp < -24 || aexp > 15) fs.flags |= 2;
@@ -315,7 +296,7 @@ __device__ __forceinline__ float emit_row(uint8_t *A, int row, int lane, const f
     a = __fmaf_rn(rf.w, rf.w, a);
     const float xx = rvq_butterfly(a);
     const FrameScale fs = frame_scale(xx, mt);
-    const float al = fs.flags ? 0.0f : ldexpf(1.0f, fs.ea);
+    const float al = fs.flags ? 0.0f : exp2i(fs.ea);
     const __half2 h0 = __floats2half2_rn(rf.x * al, rf.y * al);
     const __half2 h1 = __floats2half2_rn(rf.z * al, rf.w * al);
     const int off = (lane >> 4) * 16384 + row * 128 + ((((lane & 15) >> 1) ^ (row & 7)) << 4) + (lane & 1) * 8;
@@ -339,6 +320,7 @@ struct TcParams {
     int C, K, NT;         // NT = C / 128
     int64_t *codes;       // [K][N]
     float *scratch;       // residuals of the tiles in flight: [grid][2 slots][128 frames][128] fp32
+    float *vals;          // approximate scores of the remembered groups: [grid][2 slots][LISTCAP][128 frames][16]
     // diagnostics (optional): accumulators and per-frame scan state of CTA 0 / slot 0 / first tile
     float *dbg_acc;       // [128][C] raw accumulators of stage dbg_stage
     float *dbg_info;      // [128][8]
@@ -455,6 +437,7 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
         // this warp's 32 residual rows [frame][128] fp32 in the L2-resident scratch
         float *rs = P.scratch + ((size_t)(cta * NSLOT + slot) * TILE_M + q * 32) * 128;
         float4 *rs4 = reinterpret_cast<float4 *>(rs) + lane;  // + f * 32: this lane's 4 dims of frame f
+        float *vals = P.vals + (size_t)(cta * NSLOT + slot) * LISTCAP * TILE_M * 16;
         uint32_t items = 0;  // accumulator uses of this slot so far
         const bool direct = P.xs_d == 1 && (P.xs_b & 3) == 0 && (P.xs_t & 3) == 0 && ((uintptr_t)P.x & 15) == 0;
 
@@ -501,13 +484,13 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
                 // ---- this thread's frame (= lane): error bound, augmented operand column, hand-over
                 const FrameScale fs = frame_scale(xx, mt);
                 const int flags = fs.flags;
-                const float scale_acc = ldexpf(1.0f, fs.ea + mt.scale_exp);  // acc ~= scale_acc * (r.c - cc/2)
+                const float scale_acc = exp2i(fs.ea + mt.scale_exp);  // acc ~= scale_acc * (r.c - cc/2)
                 const float R = sqrtf(xx), cn_max = sqrtf(mt.cnorm2_max);
                 const float e16 = 0.0009765625f * scale_acc * R * cn_max;  // 2^-10: fp16 rounding of both operands
                 const float e32 = 2.384185791015625e-07f * (xx + 2.0f * R * cn_max + mt.cnorm2_max) +
                                   3.814697265625e-06f * R * cn_max;         // canonical fp32 evaluation
                 const float twodelta = 2.0002f * (1.2505f * e16 + 0.5f * scale_acc * e32 + 1.0f);
-                const __half a_aug = __float2half_rn(flags ? 0.0f : ldexpf(1.0f, fs.ea + mt.scale_exp - mt.aug_exp));
+                const __half a_aug = __float2half_rn(flags ? 0.0f : exp2i(fs.ea + mt.scale_exp - mt.aug_exp));
                 {
                     const uint32_t h = (uint32_t)__half_as_ushort(a_aug);
                     uint8_t *ar = A + 32768 + (row_l >> 3) * 256 + (row_l & 7) * 16;
@@ -518,7 +501,9 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
                 __syncwarp();
                 if (lane == 0) mbar_arrive(BAR(BAR_AREADY + slot));
 
-                // ---- scan: this thread's frame = TMEM lane row_l
+                // ---- scan: this thread's frame = TMEM lane row_l.  A group = the 16 codes of one TMEM load.
+                // A group whose maximum is within 2*delta of the running maximum is remembered: its packed
+                // (max | group id) in shared memory, its 16 approximate scores in the L2 scratch.
                 float M = -CUDART_INF_F, thr = -CUDART_INF_F;
                 int cnt = 0;
                 const bool dbg = DBG && cta == 0 && slot == 0 && first && k == P.dbg_stage;
@@ -527,7 +512,7 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
                     mbar_wait(BAR(BAR_ACCFULL + slot * 2 + buf), (items >> 1) & 1u);
                     tc_fence_after();
                     const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(slot * 256 + buf * 128);
-                    // 8 chunks of 16 columns, the load of chunk c+1 in flight while chunk c is reduced
+                    // 8 loads of 16 columns, load c+1 in flight while group c is reduced
                     uint32_t va[16], vb[16];
                     tmem_ld16(taddr, va);
 #pragma unroll
@@ -540,17 +525,20 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
                             for (int i = 0; i < 16; ++i)
                                 P.dbg_acc[(size_t)row_l * C + j * 128 + ch * 16 + i] = __uint_as_float(v[i]);
                         }
-#pragma unroll
-                        for (int g = 0; g < 2; ++g) {
-                            const float gm = group_max8(&v[8 * g]);
-                            if (gm >= thr) {
-                                if (cnt < LISTCAP)
-                                    list[cnt * TILE_M + row_l] = (__float_as_uint(gm) & ~0x7FFu) | (uint32_t)(j * 16 + ch * 2 + g);
-                                ++cnt;
+                        const float gm = fmaxf(group_max8(&v[0]), group_max8(&v[8]));
+                        if (gm >= thr) {
+                            if (cnt < LISTCAP) {
+                                list[cnt * TILE_M + row_l] = (__float_as_uint(gm) & ~0x7FFu) | (uint32_t)(j * 8 + ch);
+                                uint4 *dst = reinterpret_cast<uint4 *>(vals + ((size_t)cnt * TILE_M + row_l) * 16);
+                                dst[0] = make_uint4(v[0], v[1], v[2], v[3]);
+                                dst[1] = make_uint4(v[4], v[5], v[6], v[7]);
+                                dst[2] = make_uint4(v[8], v[9], v[10], v[11]);
+                                dst[3] = make_uint4(v[12], v[13], v[14], v[15]);
                             }
-                            M = fmaxf(M, gm);
-                            thr = M - twodelta;
+                            ++cnt;
                         }
+                        M = fmaxf(M, gm);
+                        thr = M - twodelta;
                     }
                     tc_fence_before();
                     __syncwarp();
@@ -558,54 +546,66 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
                 }
                 if (DBG && dbg) {
                     float *o = P.dbg_info + row_l * 8;
-                    o[0] = xx; o[1] = flags ? 0.0f : ldexpf(1.0f, fs.ea); o[2] = twodelta; o[3] = M; o[4] = (float)cnt;
+                    o[0] = xx; o[1] = flags ? 0.0f : exp2i(fs.ea); o[2] = twodelta; o[3] = M; o[4] = (float)cnt;
                     o[5] = (float)flags; o[6] = scale_acc; o[7] = __half2float(a_aug);
                 }
 
-                // ---- resolve, phase 1 (lane = frame): which remembered groups can still hold the winner?
-                // nh = 1: only group h0 (the common case); anything else goes to resolve_slow
-                int nh = 99;
-                uint32_t h0 = 0;
+                // ---- resolve, phase 1 (lane = frame): the codes whose approximate score is within 2*delta of
+                // the maximum are the only ones that can win.  Exactly one such code (the common case): it is
+                // the winner, no exact arithmetic needed.  2..4: re-scored exactly below.  Otherwise resolve_slow.
+                int ncand = 99, myidx = 0, c1 = 0, c2 = 0, c3 = 0;
                 if (flags == 0 && cnt <= LISTCAP) {
-                    // entries were stored with 11 mantissa bits cleared: allow for that when filtering
-                    const float keep = M - twodelta - 0.0009765625f * (fabsf(M) + twodelta);
-                    nh = 0;
+                    const float keep = M - twodelta;
+                    const float keep_packed = keep - 0.0009765625f * (fabsf(M) + twodelta);  // 11 mantissa bits were cleared
+                    ncand = 0;
                     for (int e = 0; e < cnt; ++e) {
                         const uint32_t u = list[e * TILE_M + row_l];
-                        if (__uint_as_float(u & ~0x7FFu) >= keep) {
-                            if (nh == 0) h0 = u & 0x7FFu;
-                            ++nh;
+                        if (!(__uint_as_float(u & ~0x7FFu) >= keep_packed)) continue;
+                        const int cbase = (int)(u & 0x7FFu) * 16;
+                        const float4 *src = reinterpret_cast<const float4 *>(vals + ((size_t)e * TILE_M + row_l) * 16);
+#pragma unroll
+                        for (int qd = 0; qd < 4; ++qd) {
+                            const float4 t = src[qd];
+                            const float tv[4] = {t.x, t.y, t.z, t.w};
+#pragma unroll
+                            for (int i = 0; i < 4; ++i) {
+                                if (tv[i] >= keep) {
+                                    const int col = cbase + qd * 4 + i;
+                                    if (ncand == 0) myidx = col;
+                                    else if (ncand == 1) c1 = col;
+                                    else if (ncand == 2) c2 = col;
+                                    else if (ncand == 3) c3 = col;
+                                    ++ncand;
+                                }
+                            }
                         }
                     }
+                    if (ncand == 0 || ncand > 4) ncand = 99;  // 0 cannot happen (the maximum itself qualifies)
                 }
                 __syncwarp();  // lists (written by lane = frame) are read by every lane in resolve_slow
 
-                // ---- resolve, phase 2: frame by frame, warp cooperative, exact fp32 in the canonical order,
-                // fused with the residual update and the next stage's operand row.  The rows of frame
-                // f+1's group and its residual are requested before frame f is reduced.
-                const bool more = k + 1 < K;
-                if (more) mt = P.meta[k + 1];
-                int mycode = 0;
-                float xx_next = 0.0f;
-                float4 rows[8], rf = rs4[0];
-                float cn0;
-                int g_cur = __shfl_sync(0xffffffffu, (int)h0, 0);
-                load_group(Ek, cnk, g_cur, lane, rows, cn0);
-#pragma unroll 1
-                for (int f = 0; f < 32; ++f) {
-                    const int fn = min(f + 1, 31);
-                    float4 rows_n[8], rf_n = rs4[fn * 32];
-                    float cn_n;
-                    const int g_next = __shfl_sync(0xffffffffu, (int)h0, fn);
-                    load_group(Ek, cnk, g_next, lane, rows_n, cn_n);
+                // ---- resolve, phase 2a: the frames with more than one candidate, exact fp32 in the canonical order
+                for (unsigned amb = __ballot_sync(0xffffffffu, ncand != 1); amb; amb &= amb - 1) {
+                    const int f = __ffs(amb) - 1;
+                    const int nc = __shfl_sync(0xffffffffu, ncand, f);
                     const float xf = __shfl_sync(0xffffffffu, xx, f);
-                    const int nf = __shfl_sync(0xffffffffu, nh, f);
+                    const float4 rf = rs4[f * 32];
                     int idx;
-                    if (nf == 1) {  // warp uniform
-                        float bs = rvq_score(xf, group_dots(rf, rows, lane), cn0);
-                        int bi = g_cur * 8 + ((lane >> 2) & 7);
-                        warp_argmax_quads(bs, bi);
-                        idx = bi;
+                    if (nc <= 4) {
+                        const int k0 = __shfl_sync(0xffffffffu, myidx, f), k1 = __shfl_sync(0xffffffffu, c1, f);
+                        const int k2 = __shfl_sync(0xffffffffu, c2, f), k3 = __shfl_sync(0xffffffffu, c3, f);
+                        float bs = exact_score(rf, xf, Ek, cnk, k0, lane);
+                        idx = k0;
+                        const float s1 = exact_score(rf, xf, Ek, cnk, k1, lane);
+                        if (rvq_better(s1, k1, bs, idx)) { bs = s1; idx = k1; }
+                        if (nc > 2) {
+                            const float s2 = exact_score(rf, xf, Ek, cnk, k2, lane);
+                            if (rvq_better(s2, k2, bs, idx)) { bs = s2; idx = k2; }
+                        }
+                        if (nc > 3) {
+                            const float s3 = exact_score(rf, xf, Ek, cnk, k3, lane);
+                            if (rvq_better(s3, k3, bs, idx)) { bs = s3; idx = k3; }
+                        }
                     } else {
                         const int cf = __shfl_sync(0xffffffffu, cnt, f);
                         const float Mf = __shfl_sync(0xffffffffu, M, f);
@@ -613,23 +613,48 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
                         const int ff = __shfl_sync(0xffffffffu, flags, f);
                         idx = resolve_slow(rf, xf, cf, Mf, tf, ff, list + q * 32 + f, Ek, cnk, C, lane);
                     }
-                    if (lane == f) mycode = idx;
-                    if (more) {
-                        // residual = residual - quantized (core_vq.py:394)
-                        const float4 w = __ldg(reinterpret_cast<const float4 *>(Ek + (size_t)idx * 128) + lane);
-                        rf.x = __fsub_rn(rf.x, w.x);
-                        rf.y = __fsub_rn(rf.y, w.y);
-                        rf.z = __fsub_rn(rf.z, w.z);
-                        rf.w = __fsub_rn(rf.w, w.w);
-                        rs4[f * 32] = rf;
-                        const float xv = emit_row(A, q * 32 + f, lane, rf, mt);
-                        if (lane == f) xx_next = xv;
-                    }
+                    if (lane == f) myidx = idx;
+                }
+                const int mycode = myidx;
+
+                // ---- resolve, phase 2b: residual update and the next stage's operand row, two frames per
+                // iteration, the winners' rows and the residuals of the next pair requested one pair ahead
+                const bool more = k + 1 < K;
+                float xx_next = 0.0f;
+                if (more) {
+                    mt = P.meta[k + 1];
+                    float4 w[2], rf[2];
 #pragma unroll
-                    for (int j = 0; j < 8; ++j) rows[j] = rows_n[j];
-                    cn0 = cn_n;
-                    g_cur = g_next;
-                    rf = rf_n;
+                    for (int t = 0; t < 2; ++t) {
+                        const int id = __shfl_sync(0xffffffffu, myidx, t);
+                        w[t] = __ldg(reinterpret_cast<const float4 *>(Ek + (size_t)id * 128) + lane);
+                        rf[t] = rs4[t * 32];
+                    }
+#pragma unroll 1
+                    for (int f = 0; f < 32; f += 2) {
+                        float4 w_n[2], rf_n[2];
+#pragma unroll
+                        for (int t = 0; t < 2; ++t) {
+                            const int fn = min(f + 2 + t, 31);
+                            const int id = __shfl_sync(0xffffffffu, myidx, fn);
+                            w_n[t] = __ldg(reinterpret_cast<const float4 *>(Ek + (size_t)id * 128) + lane);
+                            rf_n[t] = rs4[fn * 32];
+                        }
+#pragma unroll
+                        for (int t = 0; t < 2; ++t) {
+                            // residual = residual - quantized (core_vq.py:394)
+                            float4 rn;
+                            rn.x = __fsub_rn(rf[t].x, w[t].x);
+                            rn.y = __fsub_rn(rf[t].y, w[t].y);
+                            rn.z = __fsub_rn(rf[t].z, w[t].z);
+                            rn.w = __fsub_rn(rf[t].w, w[t].w);
+                            rs4[(f + t) * 32] = rn;
+                            const float xv = emit_row(A, q * 32 + f + t, lane, rn, mt);
+                            if (lane == f + t) xx_next = xv;
+                        }
+#pragma unroll
+                        for (int t = 0; t < 2; ++t) { w[t] = w_n[t]; rf[t] = rf_n[t]; }
+                    }
                 }
                 if (n0 + lane < P.N) P.codes[(int64_t)k * P.N + n0 + lane] = (int64_t)mycode;
                 xx = xx_next;
@@ -664,9 +689,11 @@ static int tc_grid(int64_t N, int sms) {
     return (int)(grid < 1 ? 1 : grid);
 }
 
-// workspace = [256 B: decode status word] [grid x 2 slots x 128 frames x 128 fp32: residual scratch]
+// workspace = [256 B: decode status word] [grid x 128 KB: residuals] [grid x 256 KB: remembered approximate scores]
 constexpr int64_t WS_HEADER = 256;
-constexpr int64_t WS_PER_CTA = (int64_t)NSLOT * TILE_M * 128 * 4;
+constexpr int64_t WS_R_PER_CTA = (int64_t)NSLOT * TILE_M * 128 * 4;              // residuals
+constexpr int64_t WS_V_PER_CTA = (int64_t)NSLOT * LISTCAP * TILE_M * 16 * 4;   // remembered approximate scores
+constexpr int64_t WS_PER_CTA = WS_R_PER_CTA + WS_V_PER_CTA;
 
 int64_t rvq_tc_workspace_bytes(int B, int D, int T, int K, int C) {
     (void)D; (void)K; (void)C;
@@ -697,6 +724,7 @@ static int launch_tc(const float *x, const int64_t xs[3], int B, int T, const Rv
     RVQ_REQUIRE(workspace && workspace_bytes >= WS_HEADER + WS_PER_CTA * grid && ((uintptr_t)workspace & 15) == 0,
                 RVQ_EINVAL, "rvq_encode_f32: a 16-byte aligned workspace of rvq_encode_workspace_bytes() bytes is required");
     P.scratch = reinterpret_cast<float *>((char *)workspace + WS_HEADER);
+    P.vals = reinterpret_cast<float *>((char *)workspace + WS_HEADER + WS_R_PER_CTA * grid);
     if (dbg_acc) {
         RVQ_CUDA(cudaFuncSetAttribute(rvq_encode_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_ALLOC));
         rvq_encode_tc_kernel<true><<<grid, THREADS, SM_ALLOC, stream>>>(P);

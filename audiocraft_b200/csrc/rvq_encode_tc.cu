@@ -113,6 +113,24 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
         : "r"(taddr)
         : "memory");
 }
+__device__ __forceinline__ void tmem_ld64(uint32_t taddr, uint32_t (&v)[64]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x64.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, "
+        "%32, %33, %34, %35, %36, %37, %38, %39, %40, %41, %42, %43, %44, %45, %46, %47, "
+        "%48, %49, %50, %51, %52, %53, %54, %55, %56, %57, %58, %59, %60, %61, %62, %63}, [%64];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+          "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),
+          "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
+          "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31]), "=r"(v[32]),
+          "=r"(v[33]), "=r"(v[34]), "=r"(v[35]), "=r"(v[36]), "=r"(v[37]), "=r"(v[38]), "=r"(v[39]), "=r"(v[40]),
+          "=r"(v[41]), "=r"(v[42]), "=r"(v[43]), "=r"(v[44]), "=r"(v[45]), "=r"(v[46]), "=r"(v[47]), "=r"(v[48]),
+          "=r"(v[49]), "=r"(v[50]), "=r"(v[51]), "=r"(v[52]), "=r"(v[53]), "=r"(v[54]), "=r"(v[55]), "=r"(v[56]),
+          "=r"(v[57]), "=r"(v[58]), "=r"(v[59]), "=r"(v[60]), "=r"(v[61]), "=r"(v[62]), "=r"(v[63])
+        : "r"(taddr)
+        : "memory");
+}
 __device__ __forceinline__ float max3(float a, float b, float c) {
     float r;
     asm("max.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c));
@@ -324,6 +342,7 @@ struct TcParams {
     // diagnostics (optional): accumulators and per-frame scan state of CTA 0 / slot 0 / first tile
     float *dbg_acc;       // [128][C] raw accumulators of stage dbg_stage
     float *dbg_info;      // [128][8]
+    long long *dbg_time;  // [12 warps][8] cycle counters of CTA 0
     int dbg_stage;
 };
 
@@ -366,6 +385,15 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
     const int grid = gridDim.x, cta = blockIdx.x;
     const int NT = P.NT, K = P.K;
     const int per_tile = K * NT;  // items per tile
+    // diagnostics: per-role cycle counters of CTA 0 (DBG build only), written to P.dbg_time[warp][8]
+    long long tm[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    long long t_last = DBG ? clock64() : 0;
+#define RVQ_LAP(i)                                  \
+    if (DBG) {                                      \
+        const long long t_now = clock64();          \
+        tm[i] += t_now - t_last;                    \
+        t_last = t_now;                             \
+    }
 
     if (warp < 4) {
         asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
@@ -388,8 +416,10 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
                     s = cand;
                 }
                 if (s < 0) { __nanosleep(32); continue; }
+                RVQ_LAP(0)
                 const int ridx = it % RING;
                 mbar_wait(BAR(BAR_BEMPTY + ridx), (((uint32_t)(it / RING)) & 1u) ^ 1u);
+                RVQ_LAP(1)
                 ring_meta[ridx] = (uint32_t)s;
                 const int i = s ? next1 : next0;
                 const int k = (i / NT) % K, j = i % NT;
@@ -405,12 +435,16 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
             int cnt0 = 0, cnt1 = 0;
             for (int it = 0; it < total; ++it) {
                 const int ridx = it % RING;
+                RVQ_LAP(0)
                 mbar_wait(BAR(BAR_BFULL + ridx), ((uint32_t)(it / RING)) & 1u);
+                RVQ_LAP(1)
                 const int s = (int)ring_meta[ridx];
                 const int c = s ? cnt1 : cnt0;
                 if (c % NT == 0) mbar_wait(BAR(BAR_AREADY + s), (uint32_t)(c / NT) & 1u);
+                RVQ_LAP(2)
                 const int buf = c & 1;
                 mbar_wait(BAR(BAR_ACCEMPTY + s * 2 + buf), (((uint32_t)(c >> 1)) & 1u) ^ 1u);
+                RVQ_LAP(3)
                 tc_fence_after();
                 const uint32_t d = tmem + (uint32_t)(s * 256 + buf * 128);
                 const uint32_t a = base + SM_A + s * IMG, b = base + SM_RING + ridx * IMG;
@@ -443,6 +477,7 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
 
         for (int tile = cta + grid * slot, first = 1; tile < P.ntiles; tile += 2 * grid, first = 0) {
             const int64_t n0 = (int64_t)tile * TILE_M + q * 32;
+            RVQ_LAP(0)
             // lane = frame: where this lane's frame starts in x (-1: past the end)
             const int64_t n_l = n0 + lane;
             const int64_t xoff = n_l < P.N ? (n_l / P.T) * P.xs_b + (n_l % P.T) * P.xs_t : -1;
@@ -465,19 +500,25 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
             // ---- stage 0 operand rows; lane f keeps ||r_f||^2
             RvqStageMeta mt = P.meta[0];
             float xx = 0.0f;
-            for (int f = 0; f < 32; ++f) {
-                float4 rf;
-                if (direct) {
-                    const int64_t o = __shfl_sync(0xffffffffu, xoff, f);
-                    rf = o >= 0 ? *(reinterpret_cast<const float4 *>(P.x + o) + lane) : make_float4(0.f, 0.f, 0.f, 0.f);
-                    rs4[f * 32] = rf;
-                } else {
-                    rf = rs4[f * 32];
+            for (int f0 = 0; f0 < 32; f0 += 4) {
+                float4 rf[4];
+#pragma unroll
+                for (int t = 0; t < 4; ++t) {  // four independent loads in flight
+                    if (direct) {
+                        const int64_t o = __shfl_sync(0xffffffffu, xoff, f0 + t);
+                        rf[t] = o >= 0 ? *(reinterpret_cast<const float4 *>(P.x + o) + lane) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    } else {
+                        rf[t] = rs4[(f0 + t) * 32];
+                    }
                 }
-                const float xv = emit_row(A, q * 32 + f, lane, rf, mt);
-                if (lane == f) xx = xv;
+#pragma unroll
+                for (int t = 0; t < 4; ++t) {
+                    if (direct) rs4[(f0 + t) * 32] = rf[t];
+                    const float xv = emit_row(A, q * 32 + f0 + t, lane, rf[t], mt);
+                    if (lane == f0 + t) xx = xv;
+                }
             }
-
+            RVQ_LAP(1)
             for (int k = 0; k < K; ++k) {
                 const float *Ek = P.embed + (size_t)k * C * 128;
                 const float *cnk = P.cnorm + (size_t)k * C;
@@ -507,42 +548,67 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
                 float M = -CUDART_INF_F, thr = -CUDART_INF_F;
                 int cnt = 0;
                 const bool dbg = DBG && cta == 0 && slot == 0 && first && k == P.dbg_stage;
-                for (int j = 0; j < NT; ++j, ++items) {
-                    const int buf = items & 1;
-                    mbar_wait(BAR(BAR_ACCFULL + slot * 2 + buf), (items >> 1) & 1u);
-                    tc_fence_after();
-                    const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(slot * 256 + buf * 128);
-                    // 8 loads of 16 columns, load c+1 in flight while group c is reduced
-                    uint32_t va[16], vb[16];
-                    tmem_ld16(taddr, va);
+                RVQ_LAP(2)
+                // One accumulator = 128 codes = two TMEM loads of 64 columns.  While one half is reduced the
+                // next half (of this accumulator, or of the next one if it is already complete) is in flight;
+                // the accumulator is handed back to the MMA warp as soon as both halves are in registers.
+                auto scan_half = [&](const uint32_t(&v)[64], int j, int half) {
 #pragma unroll
-                    for (int ch = 0; ch < 8; ++ch) {
-                        uint32_t(&v)[16] = (ch & 1) ? vb : va;
-                        tmem_wait_ld();
-                        if (ch + 1 < 8) tmem_ld16(taddr + (ch + 1) * 16, (ch & 1) ? va : vb);
+                    for (int g = 0; g < 4; ++g) {
+                        const uint32_t *vg = &v[16 * g];
                         if (DBG && dbg) {
 #pragma unroll
                             for (int i = 0; i < 16; ++i)
-                                P.dbg_acc[(size_t)row_l * C + j * 128 + ch * 16 + i] = __uint_as_float(v[i]);
+                                P.dbg_acc[(size_t)row_l * C + j * 128 + half * 64 + g * 16 + i] = __uint_as_float(vg[i]);
                         }
-                        const float gm = fmaxf(group_max8(&v[0]), group_max8(&v[8]));
+                        const float gm = fmaxf(group_max8(vg), group_max8(vg + 8));
                         if (gm >= thr) {
                             if (cnt < LISTCAP) {
-                                list[cnt * TILE_M + row_l] = (__float_as_uint(gm) & ~0x7FFu) | (uint32_t)(j * 8 + ch);
+                                list[cnt * TILE_M + row_l] = (__float_as_uint(gm) & ~0x7FFu) | (uint32_t)(j * 8 + half * 4 + g);
                                 uint4 *dst = reinterpret_cast<uint4 *>(vals + ((size_t)cnt * TILE_M + row_l) * 16);
-                                dst[0] = make_uint4(v[0], v[1], v[2], v[3]);
-                                dst[1] = make_uint4(v[4], v[5], v[6], v[7]);
-                                dst[2] = make_uint4(v[8], v[9], v[10], v[11]);
-                                dst[3] = make_uint4(v[12], v[13], v[14], v[15]);
+                                dst[0] = make_uint4(vg[0], vg[1], vg[2], vg[3]);
+                                dst[1] = make_uint4(vg[4], vg[5], vg[6], vg[7]);
+                                dst[2] = make_uint4(vg[8], vg[9], vg[10], vg[11]);
+                                dst[3] = make_uint4(vg[12], vg[13], vg[14], vg[15]);
                             }
                             ++cnt;
                         }
                         M = fmaxf(M, gm);
                         thr = M - twodelta;
                     }
+                };
+                const uint32_t tq = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(slot * 256);
+                uint32_t va[64], vb[64];
+                mbar_wait(BAR(BAR_ACCFULL + slot * 2 + (items & 1)), (items >> 1) & 1u);
+                tc_fence_after();
+                tmem_ld64(tq + (items & 1) * 128, va);
+                for (int j = 0; j < NT; ++j, ++items) {
+                    const int buf = items & 1;
+                    tmem_wait_ld();
+                    tmem_ld64(tq + buf * 128 + 64, vb);
+                    RVQ_LAP(3)
+                    scan_half(va, j, 0);
+                    tmem_wait_ld();
                     tc_fence_before();
                     __syncwarp();
                     if (lane == 0) mbar_arrive(BAR(BAR_ACCEMPTY + slot * 2 + buf));
+                    // next accumulator: start its first half now if it is already complete (warp uniform)
+                    const uint32_t nbar = BAR(BAR_ACCFULL + slot * 2 + (buf ^ 1)), npar = ((items + 1) >> 1) & 1u;
+                    bool started = false;
+                    if (j + 1 < NT) {
+                        started = __shfl_sync(0xffffffffu, (int)mbar_test(nbar, npar), 0) != 0;
+                        if (started) {
+                            tc_fence_after();
+                            tmem_ld64(tq + (buf ^ 1) * 128, va);
+                        }
+                    }
+                    scan_half(vb, j, 1);
+                    RVQ_LAP(4)
+                    if (j + 1 < NT && !started) {
+                        mbar_wait(nbar, npar);
+                        tc_fence_after();
+                        tmem_ld64(tq + (buf ^ 1) * 128, va);
+                    }
                 }
                 if (DBG && dbg) {
                     float *o = P.dbg_info + row_l * 8;
@@ -557,32 +623,54 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
                 if (flags == 0 && cnt <= LISTCAP) {
                     const float keep = M - twodelta;
                     const float keep_packed = keep - 0.0009765625f * (fabsf(M) + twodelta);  // 11 mantissa bits were cleared
-                    ncand = 0;
+                    // pass A (shared memory only): which remembered groups survive?  Up to 3 are examined here.
+                    int ne = 0, e0 = 0, e1 = 0, e2 = 0;
+                    uint32_t u0 = 0, u1 = 0, u2 = 0;
                     for (int e = 0; e < cnt; ++e) {
                         const uint32_t u = list[e * TILE_M + row_l];
-                        if (!(__uint_as_float(u & ~0x7FFu) >= keep_packed)) continue;
-                        const int cbase = (int)(u & 0x7FFu) * 16;
-                        const float4 *src = reinterpret_cast<const float4 *>(vals + ((size_t)e * TILE_M + row_l) * 16);
+                        if (__uint_as_float(u & ~0x7FFu) >= keep_packed) {
+                            if (ne == 0) { e0 = e; u0 = u; }
+                            else if (ne == 1) { e1 = e; u1 = u; }
+                            else if (ne == 2) { e2 = e; u2 = u; }
+                            ++ne;
+                        }
+                    }
+                    if (ne >= 1 && ne <= 3) {
+                        // pass B: one round trip to the L2 scratch for all surviving groups
+                        float4 t[3][4];
 #pragma unroll
-                        for (int qd = 0; qd < 4; ++qd) {
-                            const float4 t = src[qd];
-                            const float tv[4] = {t.x, t.y, t.z, t.w};
+                        for (int s3 = 0; s3 < 3; ++s3) {
+                            const int e = s3 == 0 ? e0 : (s3 == 1 ? e1 : e2);
+                            const float4 *src = reinterpret_cast<const float4 *>(vals + ((size_t)e * TILE_M + row_l) * 16);
 #pragma unroll
-                            for (int i = 0; i < 4; ++i) {
-                                if (tv[i] >= keep) {
-                                    const int col = cbase + qd * 4 + i;
-                                    if (ncand == 0) myidx = col;
-                                    else if (ncand == 1) c1 = col;
-                                    else if (ncand == 2) c2 = col;
-                                    else if (ncand == 3) c3 = col;
-                                    ++ncand;
+                            for (int qd = 0; qd < 4; ++qd)
+                                t[s3][qd] = s3 < ne ? src[qd] : make_float4(-CUDART_INF_F, -CUDART_INF_F, -CUDART_INF_F, -CUDART_INF_F);
+                        }
+                        ncand = 0;
+#pragma unroll
+                        for (int s3 = 0; s3 < 3; ++s3) {
+                            const int cbase = (int)((s3 == 0 ? u0 : (s3 == 1 ? u1 : u2)) & 0x7FFu) * 16;
+#pragma unroll
+                            for (int qd = 0; qd < 4; ++qd) {
+                                const float tv[4] = {t[s3][qd].x, t[s3][qd].y, t[s3][qd].z, t[s3][qd].w};
+#pragma unroll
+                                for (int i = 0; i < 4; ++i) {
+                                    if (tv[i] >= keep) {
+                                        const int col = cbase + qd * 4 + i;
+                                        if (ncand == 0) myidx = col;
+                                        else if (ncand == 1) c1 = col;
+                                        else if (ncand == 2) c2 = col;
+                                        else if (ncand == 3) c3 = col;
+                                        ++ncand;
+                                    }
                                 }
                             }
                         }
+                        if (ncand == 0 || ncand > 4) ncand = 99;  // 0 cannot happen (the maximum itself qualifies)
                     }
-                    if (ncand == 0 || ncand > 4) ncand = 99;  // 0 cannot happen (the maximum itself qualifies)
                 }
                 __syncwarp();  // lists (written by lane = frame) are read by every lane in resolve_slow
+                RVQ_LAP(5)
 
                 // ---- resolve, phase 2a: the frames with more than one candidate, exact fp32 in the canonical order
                 for (unsigned amb = __ballot_sync(0xffffffffu, ncand != 1); amb; amb &= amb - 1) {
@@ -616,6 +704,7 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
                     if (lane == f) myidx = idx;
                 }
                 const int mycode = myidx;
+                RVQ_LAP(6)
 
                 // ---- resolve, phase 2b: residual update and the next stage's operand row, two frames per
                 // iteration, the winners' rows and the residuals of the next pair requested one pair ahead
@@ -659,9 +748,14 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
                 if (n0 + lane < P.N) P.codes[(int64_t)k * P.N + n0 + lane] = (int64_t)mycode;
                 xx = xx_next;
                 __syncwarp();
+                RVQ_LAP(7)
             }
         }
     }
+    if (DBG && cta == 0 && lane == 0 && P.dbg_time) {
+        for (int i = 0; i < 8; ++i) P.dbg_time[warp * 8 + i] = tm[i];
+    }
+#undef RVQ_LAP
 
     tc_fence_before();
     __syncthreads();
@@ -717,6 +811,7 @@ static int launch_tc(const float *x, const int64_t xs[3], int B, int T, const Rv
     P.C = pv.C; P.K = K; P.NT = pv.C / 128;
     P.codes = codes;
     P.dbg_acc = dbg_acc; P.dbg_info = dbg_info; P.dbg_stage = dbg_stage;
+    P.dbg_time = dbg_info ? reinterpret_cast<long long *>(dbg_info + 128 * 8) : nullptr;  // info_out: 128*8 floats + 96 int64
     int sms = 0;
     int rc = device_sms(&sms);
     if (rc != RVQ_OK) return rc;

@@ -91,7 +91,8 @@ int rvq_decode_f32(const void *codes, int code_bytes, const int64_t cs[3], int B
 /*
  * Diagnostics (no counterpart in the reference): runs the tensor-core encode and also returns, for
  * the first 128 frames and stage `stage`, the raw approximate scores of every code
- * (acc_out, device fp32 [128][C]) and the per-frame scan state (info_out, device fp32 [128][8]:
+ * (acc_out, device fp32 [128][C]) and the per-frame scan state (info_out, device buffer of
+ * 128*8 fp32 followed by 96 int64 per-role cycle counters of CTA 0; the fp32 part is [128][8]:
  * ||r||^2, alpha, 2*delta, running maximum, remembered groups, flags, score scale, augmented-column
  * value).  Used by the tests to check the error bound that certifies the exact re-scoring.
  * workspace: as for rvq_encode_f32 with RVQ_ALGO_TC.

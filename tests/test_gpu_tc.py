@@ -22,7 +22,7 @@ def tc_scores(m, x, stage):
     K = m.n_q
     codes = torch.empty((K, B, T), dtype=torch.int64, device=x.device)
     acc = torch.full((128, C), float("nan"), device=x.device)
-    info = torch.zeros((128, 8), device=x.device)
+    info = torch.zeros((128 * 8 + 192,), device=x.device)   # 128 x 8 fp32 + 96 int64 cycle counters
     ws_bytes = lib.rvq_encode_workspace_bytes(B, D, T, K, C, _lib.ALGO_TC)
     ws = torch.empty(ws_bytes, dtype=torch.uint8, device=x.device)
     rc = lib.rvq_debug_tc_scores(x.data_ptr(), _lib.strides3(x.stride()), B, D, T, pack.data_ptr(), Ktot, C, K,
@@ -30,7 +30,7 @@ def tc_scores(m, x, stage):
                                  torch.cuda.current_stream().cuda_stream)
     _lib.check(rc, "rvq_debug_tc_scores")
     torch.cuda.synchronize()
-    return codes.cpu().numpy(), acc.cpu().numpy(), info.cpu().numpy()
+    return codes.cpu().numpy(), acc.cpu().numpy(), info[:1024].view(128, 8).cpu().numpy()
 
 
 @pytest.mark.parametrize("stage", [0, 3])

@@ -81,6 +81,18 @@ __device__ __forceinline__ bool mbar_test(uint32_t bar, uint32_t parity) {
         : "memory");
     return ok != 0;
 }
+// non-blocking probe (try_wait may suspend the thread for a while before it answers)
+__device__ __forceinline__ bool mbar_probe(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     while (!mbar_test(bar, parity)) {}
 }
@@ -412,7 +424,7 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
                     const int tot = cand ? total1 : total0;
                     if (s >= 0 || nx >= tot) continue;
                     if (cand == 1 && next1 == 0 && next0 < lead) continue;
-                    if (nx % NT == 0 && !mbar_test(BAR(BAR_AREADY + cand), (uint32_t)(nx / NT) & 1u)) continue;
+                    if (nx % NT == 0 && !mbar_probe(BAR(BAR_AREADY + cand), (uint32_t)(nx / NT) & 1u)) continue;
                     s = cand;
                 }
                 if (s < 0) { __nanosleep(32); continue; }
@@ -596,7 +608,7 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
                     const uint32_t nbar = BAR(BAR_ACCFULL + slot * 2 + (buf ^ 1)), npar = ((items + 1) >> 1) & 1u;
                     bool started = false;
                     if (j + 1 < NT) {
-                        started = __shfl_sync(0xffffffffu, (int)mbar_test(nbar, npar), 0) != 0;
+                        started = __shfl_sync(0xffffffffu, (int)mbar_probe(nbar, npar), 0) != 0;
                         if (started) {
                             tc_fence_after();
                             tmem_ld64(tq + (buf ^ 1) * 128, va);

@@ -445,6 +445,8 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
             // ============================ MMA issuer ============================
             const int total = (slot_tiles(P.ntiles, grid, cta, 0) + slot_tiles(P.ntiles, grid, cta, 1)) * per_tile;
             int cnt0 = 0, cnt1 = 0;
+            const uint64_t adesc0 = desc_sw128(base + SM_A), bdesc0 = desc_sw128(base + SM_RING);
+            const uint64_t aaug0 = desc_interleaved(base + SM_A + 32768), baug0 = desc_interleaved(base + SM_RING + 32768);
             for (int it = 0; it < total; ++it) {
                 const int ridx = it % RING;
                 RVQ_LAP(0)
@@ -459,14 +461,15 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
                 RVQ_LAP(3)
                 tc_fence_after();
                 const uint32_t d = tmem + (uint32_t)(s * 256 + buf * 128);
-                const uint32_t a = base + SM_A + s * IMG, b = base + SM_RING + ridx * IMG;
+                // descriptors: only the 14-bit start address field changes (16-byte units)
+                const uint64_t a0 = adesc0 + (uint64_t)(s * (IMG >> 4)), b0 = bdesc0 + (uint64_t)(ridx * (IMG >> 4));
 #pragma unroll
                 for (int kb = 0; kb < 2; ++kb)
 #pragma unroll
                     for (int ks = 0; ks < 4; ++ks)
-                        umma_f16(d, desc_sw128(a + kb * 16384 + ks * 32), desc_sw128(b + kb * 16384 + ks * 32), IDESC,
+                        umma_f16(d, a0 + (uint64_t)(kb * 1024 + ks * 2), b0 + (uint64_t)(kb * 1024 + ks * 2), IDESC,
                                  (kb | ks) ? 1u : 0u);
-                umma_f16(d, desc_interleaved(a + 32768), desc_interleaved(b + 32768), IDESC, 1u);
+                umma_f16(d, aaug0 + (uint64_t)(s * (IMG >> 4)), baug0 + (uint64_t)(ridx * (IMG >> 4)), IDESC, 1u);
                 umma_commit(BAR(BAR_BEMPTY + ridx));
                 umma_commit(BAR(BAR_ACCFULL + s * 2 + buf));
                 if (s) ++cnt1; else ++cnt0;
@@ -565,6 +568,9 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
                 // next half (of this accumulator, or of the next one if it is already complete) is in flight;
                 // the accumulator is handed back to the MMA warp as soon as both halves are in registers.
                 auto scan_half = [&](const uint32_t(&v)[64], int j, int half) {
+                    float gmx[4];  // the four group maxima first: independent dependency chains
+#pragma unroll
+                    for (int g = 0; g < 4; ++g) gmx[g] = fmaxf(group_max8(&v[16 * g]), group_max8(&v[16 * g + 8]));
 #pragma unroll
                     for (int g = 0; g < 4; ++g) {
                         const uint32_t *vg = &v[16 * g];
@@ -573,7 +579,7 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
                             for (int i = 0; i < 16; ++i)
                                 P.dbg_acc[(size_t)row_l * C + j * 128 + half * 64 + g * 16 + i] = __uint_as_float(vg[i]);
                         }
-                        const float gm = fmaxf(group_max8(vg), group_max8(vg + 8));
+                        const float gm = gmx[g];
                         if (gm >= thr) {
                             if (cnt < LISTCAP) {
                                 list[cnt * TILE_M + row_l] = (__float_as_uint(gm) & ~0x7FFu) | (uint32_t)(j * 8 + half * 4 + g);

@@ -55,11 +55,7 @@ rvq_decode_kernel(const void *__restrict__ codes, int64_t cs_b, int64_t cs_k, in
         const int t0 = (int)(g % tblocks) * 32;
         const int nf = min(32, T - t0);
         __syncwarp();
-        // lane = frame: coalesced read of the K codes of this lane's frame.  KT > 0: they stay in registers and
-        // are broadcast by shuffles (no shared-memory traffic: the L1 data pipe is this kernel's bottleneck)
-        int mycode[KT > 0 ? KT : 1];
-#pragma unroll
-        for (int k = 0; k < (KT > 0 ? KT : 1); ++k) mycode[k] = 0;
+        // lane = frame: coalesced read of the K codes of this lane's frame
         if (lane < nf) {
             const int64_t base = b * cs_b + (int64_t)(t0 + lane) * cs_t;
 #pragma unroll
@@ -70,8 +66,7 @@ rvq_decode_kernel(const void *__restrict__ codes, int64_t cs_b, int64_t cs_k, in
                         rvq_flag_bad_code(status, (b * K + kk) * (long long)T + t0 + lane);
                         c = 0;
                     }
-                    if (KT > 0) mycode[k] = (int)c;
-                    else wcodes[lane * KP + kk] = (int)c;
+                    wcodes[lane * KP + kk] = (int)c;
                 }
             }
         }
@@ -87,8 +82,16 @@ rvq_decode_kernel(const void *__restrict__ codes, int64_t cs_b, int64_t cs_k, in
                 float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);  // quantized_out = 0.0 (core_vq.py:400)
                 if (KT > 0) {
                     int code[8];
+                    if ((KT & 3) == 0) {
 #pragma unroll
-                    for (int j = 0; j < KT; ++j) code[j] = __shfl_sync(0xffffffffu, mycode[j], f);
+                        for (int j = 0; j < KT; j += 4) {
+                            int4 v = *reinterpret_cast<const int4 *>(fc + j);
+                            code[j] = v.x; code[j + 1] = v.y; code[j + 2] = v.z; code[j + 3] = v.w;
+                        }
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < KT; ++j) code[j] = fc[j];
+                    }
                     float4 row[8];
 #pragma unroll
                     for (int j = 0; j < KT; ++j)

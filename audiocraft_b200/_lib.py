@@ -33,6 +33,7 @@ SIGNATURES = {
     "rvq_encode_workspace_bytes": (_i64, [_i32, _i32, _i32, _i32, _i32, _i32]),
     "rvq_encode_f32": (_i32, [_vp, _i64x3, _i32, _i32, _i32, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _i64,
                               _i32, _vp]),
+    "rvq_encode_f32_static": (_i32, [_vp, _i64x3, _i32, _i32, _i32, _vp, _i32, _i32, _i32, _vp, _vp, _vp]),
     "rvq_debug_tc_scores": (_i32, [_vp, _i64x3, _i32, _i32, _i32, _vp, _i32, _i32, _i32, _i32, _vp, _vp, _vp, _vp,
                                    _i64, _vp]),
     "rvq_decode_f32": (_i32, [_vp, _i32, _i64x3, _i32, _i32, _i32, _vp, _i32, _i32, _i32, _vp, _i64x3, _vp,

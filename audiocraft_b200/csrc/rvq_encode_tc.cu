@@ -27,6 +27,8 @@
 #include <limits.h>
 #include <math_constants.h>
 
+#include <mutex>
+
 #include "rvq_common.cuh"
 
 namespace {
@@ -870,4 +872,56 @@ extern "C" int rvq_debug_tc_scores(const float *x, const int64_t xs[3], int B, i
     RvqPackView pv = rvq_pack_view(pack, Ktot, C, D);
     return launch_tc(x, xs, B, T, pv, K, codes, workspace, workspace_bytes, acc_out, info_out, stage,
                      (cudaStream_t)stream_);
+}
+
+// ------------------------------------------------------------------------------------ no-allocation entry point
+// Scratch for rvq_encode_f32_static: the same layout rvq_encode_f32 expects in its caller-provided workspace,
+// sized for RVQ_STATIC_MAX_FRAMES frames (16 CTAs of two 128-frame tiles).  It lives in the module image, so
+// every GPU that loads the library carries these ~6 MB until the process exits.
+static constexpr int STATIC_CTAS = RVQ_STATIC_MAX_FRAMES / (NSLOT * TILE_M);
+static __device__ __align__(256) unsigned char g_static_scratch[WS_HEADER + WS_PER_CTA * STATIC_CTAS];
+
+// In host code `g_static_scratch` is only a handle for the runtime, not an address a kernel can use: the device
+// address has to be asked for, once per device, with that device current.
+static int static_scratch_address(void **out) {
+    static std::mutex mu;
+    static void *cached[64] = {nullptr};
+    int dev = 0;
+    RVQ_CUDA(cudaGetDevice(&dev));
+    RVQ_REQUIRE(dev >= 0 && dev < 64, RVQ_EUNSUPPORTED, "rvq_encode_f32_static: device ordinal %d not supported", dev);
+    std::lock_guard<std::mutex> lock(mu);
+    if (!cached[dev]) {
+        void *p = nullptr;
+        RVQ_CUDA(cudaGetSymbolAddress(&p, g_static_scratch));
+        RVQ_REQUIRE(p != nullptr, RVQ_ECUDA, "rvq_encode_f32_static: no device address for the built-in scratch");
+        cached[dev] = p;
+    }
+    *out = cached[dev];
+    return RVQ_OK;
+}
+
+extern "C" int rvq_encode_f32_static(const float *x, const int64_t xs[3], int B, int D, int T, const void *pack, int Ktot,
+                                     int C, int K, int64_t *codes, float *quantized, void *stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    RVQ_REQUIRE(B >= 0 && T >= 0 && D > 0, RVQ_EINVAL, "rvq_encode_f32_static: bad sizes B=%d D=%d T=%d", B, D, T);
+    RVQ_REQUIRE(Ktot > 0 && Ktot <= RVQ_MAX_STAGES && C > 0 && K >= 0 && K <= Ktot, RVQ_EINVAL,
+                "rvq_encode_f32_static: bad codebook sizes Ktot=%d C=%d n_q=%d", Ktot, C, K);
+    const int64_t N = (int64_t)B * T;
+    RVQ_REQUIRE(N <= RVQ_STATIC_MAX_FRAMES, RVQ_EINVAL,
+                "rvq_encode_f32_static: %lld frames exceed the built-in scratch (at most %d frames per call); "
+                "use rvq_encode_f32 with a caller-provided workspace",
+                (long long)N, RVQ_STATIC_MAX_FRAMES);
+    if (N == 0 || K == 0) return RVQ_OK;
+    RVQ_REQUIRE(x && xs && pack && codes, RVQ_EINVAL, "rvq_encode_f32_static: null pointer");
+    RVQ_REQUIRE(rvq_tc_shape_supported(D, C), RVQ_EUNSUPPORTED,
+                "rvq_encode_f32_static: only the tensor-core shapes (D = 128, C a multiple of 128) use scratch; "
+                "for D=%d C=%d call rvq_encode_f32 with RVQ_ALGO_EXACT, which needs no workspace", D, C);
+    RVQ_REQUIRE(!quantized || ((uintptr_t)quantized & 15) == 0, RVQ_EINVAL, "rvq_encode_f32_static: quantized must be 16-byte aligned");
+    void *scratch = nullptr;
+    int rc = static_scratch_address(&scratch);
+    if (rc != RVQ_OK) return rc;
+    RvqPackView pv = rvq_pack_view(pack, Ktot, C, D);
+    // The array still holds what the previous call left.  The residual / score areas are fully rewritten before
+    // they are read; the status word of the gather-sum kernel must start at zero and is cleared inside rvq_encode_tc.
+    return rvq_encode_tc(x, xs, B, D, T, pack, pv, K, codes, quantized, scratch, (int64_t)sizeof(g_static_scratch), stream);
 }

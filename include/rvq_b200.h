@@ -74,6 +74,32 @@ int rvq_encode_f32(const float *x, const int64_t xs[3], int B, int D, int T, con
                    int64_t workspace_bytes, int algo, void *stream);
 
 /*
+ * rvq_encode_f32 for callers that may not allocate.  No counterpart in the reference.
+ *
+ * rvq_encode_f32 needs a workspace (the residuals and remembered scores of the frame tiles in flight), which
+ * its caller normally takes from an allocator.  Some callers have none on the request path: a serving
+ * process that planned all of its device memory at start-up and must not grow, an audio host that calls in
+ * from a real-time thread where cudaMalloc's device-wide lock and implicit synchronisation are not
+ * acceptable, or glue code that only holds raw device pointers owned by another runtime.  For them this
+ * entry point uses a scratch array built into the library image instead (about 6 MB per GPU that loads the
+ * library, held until the process exits).  It calls no cudaMalloc / cudaFree or any other allocating
+ * routine; inputs and outputs are still the caller's.
+ *
+ *   - at most RVQ_STATIC_MAX_FRAMES frames (B*T) per call; more is refused with RVQ_EINVAL and a message
+ *     that names the limit.  Only the tensor-core shapes (D == 128, C % 128 == 0, 256 <= C <= 16384) are
+ *     accepted: the exact scan (rvq_encode_f32 with RVQ_ALGO_EXACT) needs no workspace in the first place.
+ *   - the first call on each device looks up the device address of the built-in array
+ *     (cudaGetSymbolAddress) and remembers it; make that first call outside of any stream capture.
+ *   - all calls on a device share the one array, which keeps the previous call's contents (everything
+ *     that has to start from zero is cleared by the call itself): two calls that overlap on the GPU --
+ *     different streams, or different host threads -- race on it.  Serialise them on one stream.
+ * Arguments and results are those of rvq_encode_f32 (codes and, optionally, the quantized sum), bit for bit.
+ */
+#define RVQ_STATIC_MAX_FRAMES 4096
+int rvq_encode_f32_static(const float *x, const int64_t xs[3], int B, int D, int T, const void *pack,
+                          int Ktot, int C, int K, int64_t *codes, float *quantized, void *stream);
+
+/*
  * ResidualVectorQuantization.decode (core_vq.py:399-405; F.embedding gather core_vq.py:177-179):
  * out = 0.0f + E_0[c_0] + E_1[c_1] + ... in stage order.
  *   codes      device int64 (code_bytes == 8) or int32 (code_bytes == 4); element (b,k,t) at

@@ -103,6 +103,17 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void *src, uint32_t
                  "l"(src), "r"(bytes), "r"(bar)
                  : "memory");
 }
+// one lane of a converged warp (the compiler then predicates tcgen05 / bulk-copy instructions directly
+// instead of wrapping them in a per-thread serialisation loop, as it does under `if (lane == 0)`)
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "elect.sync _|p, 0xffffffff;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(pred));
+    return pred != 0;
+}
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
@@ -368,7 +379,7 @@ __device__ __forceinline__ int slot_tiles(int ntiles, int grid, int cta, int slo
 }
 
 // ------------------------------------------------------------------------------------ kernel
-template <bool DBG>
+template <bool DBG, bool TIMING>
 __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParams P) {
     extern __shared__ uint8_t smem_raw[];
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -401,9 +412,9 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
     const int per_tile = K * NT;  // items per tile
     // diagnostics: per-role cycle counters of CTA 0 (DBG build only), written to P.dbg_time[warp][8]
     long long tm[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-    long long t_last = DBG ? clock64() : 0;
+    long long t_last = TIMING ? clock64() : 0;
 #define RVQ_LAP(i)                                  \
-    if (DBG) {                                      \
+    if (TIMING) {                                   \
         const long long t_now = clock64();          \
         tm[i] += t_now - t_last;                    \
         t_last = t_now;                             \
@@ -443,8 +454,8 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
                 last = s;
                 ++it;
             }
-        } else if (warp == 1 && lane == 0) {
-            // ============================ MMA issuer ============================
+        } else if (warp == 1) {
+            // ============================ MMA issuer (whole warp waits, one elected lane issues) ============================
             const int total = (slot_tiles(P.ntiles, grid, cta, 0) + slot_tiles(P.ntiles, grid, cta, 1)) * per_tile;
             int cnt0 = 0, cnt1 = 0;
             const uint64_t adesc0 = desc_sw128(base + SM_A), bdesc0 = desc_sw128(base + SM_RING);
@@ -465,15 +476,18 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
                 const uint32_t d = tmem + (uint32_t)(s * 256 + buf * 128);
                 // descriptors: only the 14-bit start address field changes (16-byte units)
                 const uint64_t a0 = adesc0 + (uint64_t)(s * (IMG >> 4)), b0 = bdesc0 + (uint64_t)(ridx * (IMG >> 4));
+                if (elect_one()) {
 #pragma unroll
-                for (int kb = 0; kb < 2; ++kb)
+                    for (int kb = 0; kb < 2; ++kb)
 #pragma unroll
-                    for (int ks = 0; ks < 4; ++ks)
-                        umma_f16(d, a0 + (uint64_t)(kb * 1024 + ks * 2), b0 + (uint64_t)(kb * 1024 + ks * 2), IDESC,
-                                 (kb | ks) ? 1u : 0u);
-                umma_f16(d, aaug0 + (uint64_t)(s * (IMG >> 4)), baug0 + (uint64_t)(ridx * (IMG >> 4)), IDESC, 1u);
-                umma_commit(BAR(BAR_BEMPTY + ridx));
-                umma_commit(BAR(BAR_ACCFULL + s * 2 + buf));
+                        for (int ks = 0; ks < 4; ++ks)
+                            umma_f16(d, a0 + (uint64_t)(kb * 1024 + ks * 2), b0 + (uint64_t)(kb * 1024 + ks * 2), IDESC,
+                                     (kb | ks) ? 1u : 0u);
+                    umma_f16(d, aaug0 + (uint64_t)(s * (IMG >> 4)), baug0 + (uint64_t)(ridx * (IMG >> 4)), IDESC, 1u);
+                    umma_commit(BAR(BAR_BEMPTY + ridx));
+                    umma_commit(BAR(BAR_ACCFULL + s * 2 + buf));
+                }
+                __syncwarp();
                 if (s) ++cnt1; else ++cnt0;
             }
         }
@@ -569,10 +583,14 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
                 // One accumulator = 128 codes = two TMEM loads of 64 columns.  While one half is reduced the
                 // next half (of this accumulator, or of the next one if it is already complete) is in flight;
                 // the accumulator is handed back to the MMA warp as soon as both halves are in registers.
-                auto scan_half = [&](const uint32_t(&v)[64], int j, int half) {
-                    float gmx[4];  // the four group maxima first: independent dependency chains
+                // group maxima of one 64-column half (independent dependency chains)
+                auto half_max = [&](const uint32_t(&v)[64], float(&gmx)[4]) {
 #pragma unroll
                     for (int g = 0; g < 4; ++g) gmx[g] = fmaxf(group_max8(&v[16 * g]), group_max8(&v[16 * g + 8]));
+                };
+                // remember the groups of one half that are within 2*delta of the maximum seen so far
+                // (which already includes this whole accumulator)
+                auto remember = [&](const uint32_t(&v)[64], const float(&gmx)[4], int j, int half) {
 #pragma unroll
                     for (int g = 0; g < 4; ++g) {
                         const uint32_t *vg = &v[16 * g];
@@ -581,10 +599,10 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
                             for (int i = 0; i < 16; ++i)
                                 P.dbg_acc[(size_t)row_l * C + j * 128 + half * 64 + g * 16 + i] = __uint_as_float(vg[i]);
                         }
-                        const float gm = gmx[g];
-                        if (gm >= thr) {
+                        if (gmx[g] >= thr) {
                             if (cnt < LISTCAP) {
-                                list[cnt * TILE_M + row_l] = (__float_as_uint(gm) & ~0x7FFu) | (uint32_t)(j * 8 + half * 4 + g);
+                                list[cnt * TILE_M + row_l] =
+                                    (__float_as_uint(gmx[g]) & ~0x7FFu) | (uint32_t)(j * 8 + half * 4 + g);
                                 uint4 *dst = reinterpret_cast<uint4 *>(vals + ((size_t)cnt * TILE_M + row_l) * 16);
                                 dst[0] = make_uint4(vg[0], vg[1], vg[2], vg[3]);
                                 dst[1] = make_uint4(vg[4], vg[5], vg[6], vg[7]);
@@ -593,8 +611,6 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
                             }
                             ++cnt;
                         }
-                        M = fmaxf(M, gm);
-                        thr = M - twodelta;
                     }
                 };
                 const uint32_t tq = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(slot * 256);
@@ -604,14 +620,21 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
                 tmem_ld64(tq + (items & 1) * 128, va);
                 for (int j = 0; j < NT; ++j, ++items) {
                     const int buf = items & 1;
+                    float ga[4], gb[4];
                     tmem_wait_ld();
                     tmem_ld64(tq + buf * 128 + 64, vb);
                     RVQ_LAP(3)
-                    scan_half(va, j, 0);
+                    half_max(va, ga);
                     tmem_wait_ld();
                     tc_fence_before();
                     __syncwarp();
                     if (lane == 0) mbar_arrive(BAR(BAR_ACCEMPTY + slot * 2 + buf));
+                    half_max(vb, gb);
+                    // the threshold uses the maximum over everything up to and including this accumulator
+                    M = fmaxf(M, fmaxf(max3(ga[0], ga[1], ga[2]), max3(ga[3], gb[0], gb[1])));
+                    M = max3(M, gb[2], gb[3]);
+                    thr = M - twodelta;
+                    remember(va, ga, j, 0);
                     // next accumulator: start its first half now if it is already complete (warp uniform)
                     const uint32_t nbar = BAR(BAR_ACCFULL + slot * 2 + (buf ^ 1)), npar = ((items + 1) >> 1) & 1u;
                     bool started = false;
@@ -622,7 +645,7 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
                             tmem_ld64(tq + (buf ^ 1) * 128, va);
                         }
                     }
-                    scan_half(vb, j, 1);
+                    remember(vb, gb, j, 1);
                     RVQ_LAP(4)
                     if (j + 1 < NT && !started) {
                         mbar_wait(nbar, npar);
@@ -772,7 +795,7 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
             }
         }
     }
-    if (DBG && cta == 0 && lane == 0 && P.dbg_time) {
+    if (TIMING && cta == 0 && lane == 0 && P.dbg_time) {
         for (int i = 0; i < 8; ++i) P.dbg_time[warp * 8 + i] = tm[i];
     }
 #undef RVQ_LAP
@@ -841,11 +864,14 @@ static int launch_tc(const float *x, const int64_t xs[3], int B, int T, const Rv
     P.scratch = reinterpret_cast<float *>((char *)workspace + WS_HEADER);
     P.vals = reinterpret_cast<float *>((char *)workspace + WS_HEADER + WS_R_PER_CTA * grid);
     if (dbg_acc) {
-        RVQ_CUDA(cudaFuncSetAttribute(rvq_encode_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_ALLOC));
-        rvq_encode_tc_kernel<true><<<grid, THREADS, SM_ALLOC, stream>>>(P);
+        RVQ_CUDA(cudaFuncSetAttribute(rvq_encode_tc_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_ALLOC));
+        rvq_encode_tc_kernel<true, true><<<grid, THREADS, SM_ALLOC, stream>>>(P);
+    } else if (dbg_info) {  // cycle counters only: the production code path plus clock reads
+        RVQ_CUDA(cudaFuncSetAttribute(rvq_encode_tc_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_ALLOC));
+        rvq_encode_tc_kernel<false, true><<<grid, THREADS, SM_ALLOC, stream>>>(P);
     } else {
-        RVQ_CUDA(cudaFuncSetAttribute(rvq_encode_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_ALLOC));
-        rvq_encode_tc_kernel<false><<<grid, THREADS, SM_ALLOC, stream>>>(P);
+        RVQ_CUDA(cudaFuncSetAttribute(rvq_encode_tc_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_ALLOC));
+        rvq_encode_tc_kernel<false, false><<<grid, THREADS, SM_ALLOC, stream>>>(P);
     }
     rvq_count_launch(1);
     return rvq_check_launch("rvq_encode_tc_kernel");
@@ -866,7 +892,7 @@ int rvq_encode_tc(const float *x, const int64_t xs[3], int B, int D, int T, cons
 extern "C" int rvq_debug_tc_scores(const float *x, const int64_t xs[3], int B, int D, int T, const void *pack, int Ktot,
                                    int C, int K, int stage, int64_t *codes, float *acc_out, float *info_out,
                                    void *workspace, int64_t workspace_bytes, void *stream_) {
-    RVQ_REQUIRE(x && xs && pack && codes && acc_out && info_out, RVQ_EINVAL, "rvq_debug_tc_scores: null pointer");
+    RVQ_REQUIRE(x && xs && pack && codes && info_out, RVQ_EINVAL, "rvq_debug_tc_scores: null pointer");
     RVQ_REQUIRE(rvq_tc_shape_supported(D, C) && K > 0 && K <= Ktot && stage >= 0 && stage < K, RVQ_EUNSUPPORTED,
                 "rvq_debug_tc_scores: shape not covered by the tensor-core path");
     RvqPackView pv = rvq_pack_view(pack, Ktot, C, D);

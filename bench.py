@@ -43,6 +43,25 @@ def log(*a):
     print(*a, file=sys.stderr, flush=True)
 
 
+# Rank 0 must print exactly one JSON line on stdout.  Libraries (NCCL's version banner, for one) also write
+# to file descriptor 1, so the real stdout is set aside and fd 1 is pointed at stderr for the rest of the run.
+_REAL_STDOUT = None
+
+
+def claim_stdout():
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.fdopen(os.dup(1), "w")
+        os.dup2(2, 1)
+
+
+def emit(line: dict):
+    out = _REAL_STDOUT if _REAL_STDOUT is not None else sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
+
+
 def measured_peaks():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(path):
@@ -167,7 +186,7 @@ def run_reference_arm(args, rank: int):
         "e2e": {"value": round(value, 6), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
     return 0
 
 
@@ -353,7 +372,7 @@ def run_gpu_arm(args, rank: int, world: int, local_rank: int):
                     "decode_mframes_per_s": round(frames / dec_ms / 1e3, 3)},
         "decode_c4": dec_c4,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
     return 0
@@ -374,6 +393,7 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+    claim_stdout()
     if args.impl == "reference":
         return run_reference_arm(args, rank)
     if world != args.gpus:

@@ -121,6 +121,7 @@ int rvq_decode_f32(const void *codes, int code_bytes, const int64_t cs[3], int B
  * 128*8 fp32 followed by 96 int64 per-role cycle counters of CTA 0; the fp32 part is [128][8]:
  * ||r||^2, alpha, 2*delta, running maximum, remembered groups, flags, score scale, augmented-column
  * value).  Used by the tests to check the error bound that certifies the exact re-scoring.
+ * acc_out may be NULL: then only the cycle counters are collected, on the production code path.
  * workspace: as for rvq_encode_f32 with RVQ_ALGO_TC.
  */
 int rvq_debug_tc_scores(const float *x, const int64_t xs[3], int B, int D, int T, const void *pack,

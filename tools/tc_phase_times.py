@@ -21,11 +21,18 @@ ws_bytes = lib.rvq_encode_workspace_bytes(B, D, T, K, C, _lib.ALGO_TC)
 ws = torch.empty(ws_bytes, dtype=torch.uint8, device="cuda")
 for _ in range(3):
     rc = lib.rvq_debug_tc_scores(x.data_ptr(), _lib.strides3(x.stride()), B, D, T, pack.data_ptr(), Ktot, C, K, 0,
-                                 codes.data_ptr(), acc.data_ptr(), info.data_ptr(), ws.data_ptr(), ws_bytes,
+                                 codes.data_ptr(), None, info.data_ptr(), ws.data_ptr(), ws_bytes,
                                  torch.cuda.current_stream().cuda_stream)
     _lib.check(rc, "debug")
     torch.cuda.synchronize()
 t = info[1024:].view(torch.int64).view(12, 8).cpu().numpy()
+a = torch.cuda.Event(enable_timing=True); b = torch.cuda.Event(enable_timing=True)
+a.record()
+lib.rvq_debug_tc_scores(x.data_ptr(), _lib.strides3(x.stride()), B, D, T, pack.data_ptr(), Ktot, C, K, 0,
+                        codes.data_ptr(), None, info.data_ptr(), ws.data_ptr(), ws_bytes,
+                        torch.cuda.current_stream().cuda_stream)
+b.record(); torch.cuda.synchronize()
+print("timing build kernel: %.3f ms" % a.elapsed_time(b))
 names = {0: ["loop", "wait b_empty"], 1: ["loop", "wait b_full", "wait a_ready", "wait acc_empty", "", "", "", ""]}
 print("producer  :", dict(zip(["issue", "wait_b_empty"], t[0][:2])))
 print("mma       :", dict(zip(["issue", "wait_b_full", "wait_a_ready", "wait_acc_empty"], t[1][:4])))

@@ -272,27 +272,27 @@ def run_gpu_arm(args, rank: int, world: int, local_rank: int):
     elapsed_ms = float(t.item())
 
     # ---- end to end through the public API with host buffers ---------------------------------
+    # audiocraft_b200.host_pipeline.HostPipeline: pinned host latents in, pinned host codes + quantized latents
+    # out, chunked over copy / compute / copy streams.  Every byte of every step crosses PCIe inside the timed region.
+    from audiocraft_b200.host_pipeline import HostPipeline
+    pipe = HostPipeline(m, dev, chunk_items=16)
     x_host = [torch.randn(B, D, T).pin_memory() for _ in range(2)]
-    codes_host = torch.empty((B, K, T), dtype=torch.int64).pin_memory()
-    q_host = torch.empty((B, T, D), dtype=torch.float32).pin_memory()
-    x_dev = torch.empty((B, D, T), device=dev)
-
-    def e2e_step(i):
-        x_dev.copy_(x_host[i % 2], non_blocking=True)
-        codes = m.encode(x_dev)
-        q = m.decode(codes)
-        codes_host.copy_(codes, non_blocking=True)
-        q_host.copy_(q.transpose(1, 2), non_blocking=True)  # physical [B, T, D]
+    codes_host = [torch.empty((B, K, T), dtype=torch.int64).pin_memory() for _ in range(2)]
+    q_host = [torch.empty((B, T, D), dtype=torch.float32).pin_memory() for _ in range(2)]
 
     with torch.no_grad():
         for i in range(min(3, args.warmup)):
-            e2e_step(i)
+            pipe.encode_decode(x_host[i % 2], codes_host[i % 2], q_host[i % 2])
+        pipe.synchronize()
         sync_all()
         s2, e2 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         s2.record()
+        last = None
         for i in range(args.steps):
-            e2e_step(i)
+            last = pipe.encode_decode(x_host[i % 2], codes_host[i % 2], q_host[i % 2])
+        torch.cuda.current_stream(dev).wait_event(last)
         e2.record()
+        pipe.synchronize()
         sync_all()
     e2e_ms = s2.elapsed_time(e2)
     t = torch.tensor([e2e_ms], dtype=torch.float64, device=dev)

@@ -749,43 +749,48 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
                 const int mycode = myidx;
                 RVQ_LAP(6)
 
-                // ---- resolve, phase 2b: residual update and the next stage's operand row, two frames per
-                // iteration, the winners' rows and the residuals of the next pair requested one pair ahead
+                // ---- resolve, phase 2b: residual update and the next stage's operand row, four frames per
+                // iteration (independent dependency chains side by side), the winners' rows and the residuals
+                // of the next four requested one iteration ahead
                 const bool more = k + 1 < K;
                 float xx_next = 0.0f;
                 if (more) {
+                    constexpr int NB = 4;
                     mt = P.meta[k + 1];
-                    float4 w[2], rf[2];
+                    float4 w[NB], rf[NB];
 #pragma unroll
-                    for (int t = 0; t < 2; ++t) {
+                    for (int t = 0; t < NB; ++t) {
                         const int id = __shfl_sync(0xffffffffu, myidx, t);
                         w[t] = __ldg(reinterpret_cast<const float4 *>(Ek + (size_t)id * 128) + lane);
                         rf[t] = rs4[t * 32];
                     }
 #pragma unroll 1
-                    for (int f = 0; f < 32; f += 2) {
-                        float4 w_n[2], rf_n[2];
+                    for (int f = 0; f < 32; f += NB) {
+                        float4 w_n[NB], rf_n[NB];
 #pragma unroll
-                        for (int t = 0; t < 2; ++t) {
-                            const int fn = min(f + 2 + t, 31);
+                        for (int t = 0; t < NB; ++t) {
+                            const int fn = min(f + NB + t, 31);
                             const int id = __shfl_sync(0xffffffffu, myidx, fn);
                             w_n[t] = __ldg(reinterpret_cast<const float4 *>(Ek + (size_t)id * 128) + lane);
                             rf_n[t] = rs4[fn * 32];
                         }
+                        float4 rn[NB];
 #pragma unroll
-                        for (int t = 0; t < 2; ++t) {
+                        for (int t = 0; t < NB; ++t) {
                             // residual = residual - quantized (core_vq.py:394)
-                            float4 rn;
-                            rn.x = __fsub_rn(rf[t].x, w[t].x);
-                            rn.y = __fsub_rn(rf[t].y, w[t].y);
-                            rn.z = __fsub_rn(rf[t].z, w[t].z);
-                            rn.w = __fsub_rn(rf[t].w, w[t].w);
-                            rs4[(f + t) * 32] = rn;
-                            const float xv = emit_row(A, q * 32 + f + t, lane, rn, mt);
+                            rn[t].x = __fsub_rn(rf[t].x, w[t].x);
+                            rn[t].y = __fsub_rn(rf[t].y, w[t].y);
+                            rn[t].z = __fsub_rn(rf[t].z, w[t].z);
+                            rn[t].w = __fsub_rn(rf[t].w, w[t].w);
+                            rs4[(f + t) * 32] = rn[t];
+                        }
+#pragma unroll
+                        for (int t = 0; t < NB; ++t) {
+                            const float xv = emit_row(A, q * 32 + f + t, lane, rn[t], mt);
                             if (lane == f + t) xx_next = xv;
                         }
 #pragma unroll
-                        for (int t = 0; t < 2; ++t) { w[t] = w_n[t]; rf[t] = rf_n[t]; }
+                        for (int t = 0; t < NB; ++t) { w[t] = w_n[t]; rf[t] = rf_n[t]; }
                     }
                 }
                 if (n0 + lane < P.N) P.codes[(int64_t)k * P.N + n0 + lane] = (int64_t)mycode;

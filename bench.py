@@ -336,9 +336,15 @@ def run_gpu_arm(args, rank: int, world: int, local_rank: int):
     value = total_frames / (elapsed_ms * 1e-3) / 1e6
     enc_flops = 2.0 * D * C * K * frames  # algorithmic: the ||x||^2 - 2 x.c + ||c||^2 contraction only
     achieved_tf = enc_flops / (enc_ms * 1e-3) / 1e12
+    traffic = None
+    try:  # DRAM bytes per launch of the encode kernel from the committed ncu --set full capture (profiles/)
+        with open(os.path.join(ROOT, "profiles", "r1_traffic.json")) as f:
+            traffic = json.load(f).get("rvq_encode_tc_kernel_config2_bytes")
+    except Exception:
+        pass
     roofline = {"bound": "tensor", "kernel": "rvq_encode (all stages fused)", "achieved": round(achieved_tf, 3),
                 "peak": peaks["bf16"], "unit": "TFLOP/s", "frac": round(achieved_tf / peaks["bf16"], 5),
-                "traffic": None, "peak_source": peaks["source"] + ", dense bf16 burst",
+                "traffic": traffic, "peak_source": peaks["source"] + ", dense bf16 burst",
                 "us_per_launch": round(enc_ms * 1e3, 2)}
     if dec_c4 is not None:
         dec_c4["peak_gbs"] = peaks["hbm"]

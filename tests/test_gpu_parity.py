@@ -286,3 +286,45 @@ def test_abi_rejects_bad_arguments():
     assert lib.rvq_encode_f32(None, st, 1, 130, 1, None, 4, 2048, 4, None, None, None, 0, 0, None) != 0
     assert lib.rvq_decode_f32(None, 2, st, 1, 1, 1, None, 4, 2048, 128, None, st, None, None) == _lib.RVQ_EINVAL
     assert kernels.launch_count() >= 0
+
+
+def test_full_size_c3_deep_residual_properties():
+    """BASELINE config 3 at full size (K=32, C=1024, 64 x 2250 frames): prefix property of the greedy chain,
+    forward == decode(encode), and a 1-in-32 sample of the batch items against the oracle."""
+    torch.manual_seed(0)
+    m = ResidualVectorQuantizer(dimension=128, n_q=32, bins=1024, kmeans_init=False).cuda().eval()
+    g = torch.Generator(device="cuda").manual_seed(1234)
+    x = torch.randn(64, 128, 2250, device="cuda", generator=g)
+    with torch.no_grad():
+        codes = m.encode(x)
+        res = m(x, 75)
+        m.set_num_codebooks(8)
+        codes8 = m.encode(x)
+        m.set_num_codebooks(32)
+    assert codes.shape == (64, 32, 2250) and torch.equal(res.codes, codes)
+    assert torch.equal(codes8, codes[:, :8])
+    with torch.no_grad():
+        assert torch.equal(res.x, m.decode(codes))
+    embed = [l._codebook.embed.cpu().numpy() for l in m.vq.layers]
+    assert np.array_equal(codes[::32].cpu().numpy(), oracle.encode(x[::32].cpu().numpy(), embed))
+
+
+def test_c5_shard_size_properties():
+    """One rank's share of BASELINE config 5 at 8 GPUs (K=8, 2^21 frames): encoding the shard equals encoding its
+    pieces; exact and tensor-core paths agree on a slice; sampled oracle check."""
+    torch.manual_seed(0)
+    m = ResidualVectorQuantizer(dimension=128, n_q=8, bins=2048, kmeans_init=False).cuda().eval()
+    g = torch.Generator(device="cuda").manual_seed(1234 + 3)
+    x = torch.randn(1024, 128, 2048, device="cuda", generator=g)
+    with torch.no_grad():
+        codes = m.encode(x)
+        parts = torch.cat([m.encode(x[i:i + 256]) for i in range(0, 1024, 256)], dim=0)
+        assert torch.equal(codes, parts)
+        m.vq.encode_algo = "exact"
+        assert torch.equal(m.encode(x[:16]), codes[:16])
+        m.vq.encode_algo = "auto"
+        q = m.decode(codes[:64])
+    assert q.shape == (64, 128, 2048)
+    embed = [l._codebook.embed.cpu().numpy() for l in m.vq.layers]
+    sl = x[5:6, :, :512].cpu().numpy()
+    assert np.array_equal(codes[5:6, :, :512].cpu().numpy(), oracle.encode(sl, embed))

@@ -8,7 +8,7 @@ bool rvq_tc_shape_supported(int D, int C);
 int64_t rvq_tc_workspace_bytes(int B, int D, int T, int K, int C);
 int rvq_encode_tc(const float *x, const int64_t xs[3], int B, int D, int T, const void *pack, const RvqPackView &pv,
                   int K, int64_t *codes, float *quantized, void *workspace, int64_t workspace_bytes,
-                  cudaStream_t stream);
+                  cudaStream_t stream, bool fit_grid_to_workspace = false);
 
 extern "C" int64_t rvq_encode_workspace_bytes(int B, int D, int T, int K, int C, int algo) {
     if (B < 0 || D <= 0 || T < 0 || K < 0 || C <= 0) return RVQ_EINVAL;

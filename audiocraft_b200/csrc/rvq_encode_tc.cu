@@ -816,9 +816,10 @@ static int device_sms(int *sms) {
 }
 
 static int tc_grid(int64_t N, int sms) {
+    // one CTA per SM; with fewer tiles than SMs every tile gets a CTA of its own (its second slot stays idle),
+    // which halves the latency of small inputs
     const int64_t ntiles = (N + TILE_M - 1) / TILE_M;
-    int64_t grid = (ntiles + NSLOT - 1) / NSLOT;
-    if (grid > sms) grid = sms;
+    int64_t grid = ntiles < sms ? ntiles : sms;
     return (int)(grid < 1 ? 1 : grid);
 }
 
@@ -840,7 +841,7 @@ int rvq_decode_launch_internal(const int64_t *codes_kbt, int B, int K, int T, co
 
 static int launch_tc(const float *x, const int64_t xs[3], int B, int T, const RvqPackView &pv, int K, int64_t *codes,
                      void *workspace, int64_t workspace_bytes, float *dbg_acc, float *dbg_info, int dbg_stage,
-                     cudaStream_t stream) {
+                     cudaStream_t stream, bool fit_grid_to_workspace = false) {
     TcParams P;
     P.x = x; P.xs_b = xs[0]; P.xs_d = xs[1]; P.xs_t = xs[2];
     P.B = B; P.T = T; P.N = (int64_t)B * T;
@@ -854,8 +855,12 @@ static int launch_tc(const float *x, const int64_t xs[3], int B, int T, const Rv
     int sms = 0;
     int rc = device_sms(&sms);
     if (rc != RVQ_OK) return rc;
-    const int grid = tc_grid(P.N, sms);
-    RVQ_REQUIRE(workspace && workspace_bytes >= WS_HEADER + WS_PER_CTA * grid && ((uintptr_t)workspace & 15) == 0,
+    int grid = tc_grid(P.N, sms);
+    if (fit_grid_to_workspace) {  // fewer CTAs than SMs: every CTA simply walks more tiles
+        const int64_t cap = (workspace_bytes - WS_HEADER) / WS_PER_CTA;
+        if (cap < grid) grid = (int)cap;
+    }
+    RVQ_REQUIRE(workspace && grid >= 1 && workspace_bytes >= WS_HEADER + WS_PER_CTA * grid && ((uintptr_t)workspace & 15) == 0,
                 RVQ_EINVAL, "rvq_encode_f32: a 16-byte aligned workspace of rvq_encode_workspace_bytes() bytes is required");
     P.scratch = reinterpret_cast<float *>((char *)workspace + WS_HEADER);
     P.vals = reinterpret_cast<float *>((char *)workspace + WS_HEADER + WS_R_PER_CTA * grid);
@@ -875,9 +880,10 @@ static int launch_tc(const float *x, const int64_t xs[3], int B, int T, const Rv
 
 int rvq_encode_tc(const float *x, const int64_t xs[3], int B, int D, int T, const void *pack, const RvqPackView &pv,
                   int K, int64_t *codes, float *quantized, void *workspace, int64_t workspace_bytes,
-                  cudaStream_t stream) {
+                  cudaStream_t stream, bool fit_grid_to_workspace) {
     (void)pack; (void)D;
-    int rc = launch_tc(x, xs, B, T, pv, K, codes, workspace, workspace_bytes, nullptr, nullptr, 0, stream);
+    int rc = launch_tc(x, xs, B, T, pv, K, codes, workspace, workspace_bytes, nullptr, nullptr, 0, stream,
+                       fit_grid_to_workspace);
     if (rc != RVQ_OK || !quantized) return rc;
     // quantized_out = 0 + q_0 + ... (core_vq.py:363-385): the gather-sum kernel on the codes just written
     RVQ_CUDA(cudaMemsetAsync(workspace, 0, 16, stream));
@@ -945,5 +951,6 @@ extern "C" int rvq_encode_f32_static(const float *x, const int64_t xs[3], int B,
     RvqPackView pv = rvq_pack_view(pack, Ktot, C, D);
     // The array still holds what the previous call left.  The residual / score areas are fully rewritten before
     // they are read; the status word of the gather-sum kernel must start at zero and is cleared inside rvq_encode_tc.
-    return rvq_encode_tc(x, xs, B, D, T, pack, pv, K, codes, quantized, scratch, (int64_t)sizeof(g_static_scratch), stream);
+    return rvq_encode_tc(x, xs, B, D, T, pack, pv, K, codes, quantized, scratch, (int64_t)sizeof(g_static_scratch), stream,
+                         /*fit_grid_to_workspace=*/true);
 }

@@ -378,9 +378,11 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t bar0 = base + SM_BAR;
     auto BAR = [&](int i) { return bar0 + 8u * (uint32_t)i; };
-    volatile uint32_t *ring_meta = reinterpret_cast<volatile uint32_t *>(sm + SM_META);
+    // fifo[slot][4]: producer -> MMA warp of the slot, (sequence number << 16) | (ring parity << 8) | ring entry
+    volatile uint32_t *fifo = reinterpret_cast<volatile uint32_t *>(sm + SM_META + 32);
     volatile uint32_t *tmem_slot = reinterpret_cast<volatile uint32_t *>(sm + SM_META + 16);
 
+    if (threadIdx.x < NSLOT * 4) fifo[threadIdx.x] = 0u;
     if (threadIdx.x == 0) {
         for (int i = 0; i < RING; ++i) { mbar_init(BAR(BAR_BFULL + i), 1); mbar_init(BAR(BAR_BEMPTY + i), 1); }
         for (int i = 0; i < 4; ++i) { mbar_init(BAR(BAR_ACCFULL + i), 1); mbar_init(BAR(BAR_ACCEMPTY + i), 4); }
@@ -404,82 +406,133 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
     // diagnostics: per-role cycle counters of CTA 0 (DBG build only), written to P.dbg_time[warp][8]
     long long tm[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     long long t_last = TIMING ? clock64() : 0;
+#ifdef RVQ_TIMELINE
+#define RVQ_LAP(i)
+#else
 #define RVQ_LAP(i)                                  \
     if (TIMING) {                                   \
         const long long t_now = clock64();          \
         tm[i] += t_now - t_last;                    \
         t_last = t_now;                             \
     }
+#endif
+
+#ifdef RVQ_TIMELINE
+    // tools/tc_timeline.py: (tag, clock) pairs of CTA 0, lane 0 of every warp, into the buffer passed as acc_out
+    int tl_n = 0;
+#define RVQ_TL(tag)                                                                        \
+    if (cta == 0 && lane == 0 && P.dbg_acc) {                                              \
+        long long *e = reinterpret_cast<long long *>(P.dbg_acc) + ((size_t)warp * 4096 + tl_n) * 2; \
+        e[0] = (long long)(tag);                                                           \
+        e[1] = clock64();                                                                  \
+        if (tl_n < 4095) ++tl_n;                                                           \
+    }
+#else
+#define RVQ_TL(tag)
+#endif
 
     if (warp < 4) {
         asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
-        if (warp == 0 && lane == 0) {
-            // ============================ producer ============================
-            const int total0 = slot_tiles(P.ntiles, grid, cta, 0) * per_tile;
-            const int total1 = slot_tiles(P.ntiles, grid, cta, 1) * per_tile;
-            const int lead = min(NT / 2, total0);  // slot 1 starts half a stage behind slot 0
-            int next0 = 0, next1 = 0, it = 0, last = 1;
-            while (next0 < total0 || next1 < total1) {
+        if (warp == 0) {
+            // ============================ producer (whole warp, one elected lane issues) ============================
+            // Per slot: how many codebook tiles were requested so far, where in the stage / the image the next
+            // one is, and whether the slot's operand rows of the current stage are known to be complete.  Tile 0
+            // of a stage is requested before they are (the MMA warp of the slot waits for them itself), so that
+            // the first accumulator of the stage does not pay for the copy.
+            // (scalars, not arrays: the slot index is a run-time value and arrays would live in local memory)
+            const int tot0 = slot_tiles(P.ntiles, grid, cta, 0) * per_tile, tot1 = slot_tiles(P.ntiles, grid, cta, 1) * per_tile;
+            int nx0 = 0, nx1 = 0, jj0 = 0, jj1 = 0, ii0 = 0, ii1 = 0;
+            uint32_t stg0 = 0, stg1 = 0;
+            bool open0 = false, open1 = false;
+            const int lead = min(NT / 2, tot0);  // slot 1 starts half a stage behind slot 0
+            int last = 1, rnext = 0;
+            uint32_t upar = 0;  // bit e: parity of the number of tiles ring entry e has held so far
+            while (nx0 < tot0 || nx1 < tot1) {
                 int s = -1;
 #pragma unroll
                 for (int attempt = 0; attempt < 2; ++attempt) {
                     const int cand = attempt == 0 ? (last ^ 1) : last;
-                    const int nx = cand ? next1 : next0;
-                    const int tot = cand ? total1 : total0;
-                    if (s >= 0 || nx >= tot) continue;
-                    if (cand == 1 && next1 == 0 && next0 < lead) continue;
-                    if (nx % NT == 0 && !mbar_probe(BAR(BAR_AREADY + cand), (uint32_t)(nx / NT) & 1u)) continue;
+                    if (s >= 0 || (cand ? nx1 >= tot1 : nx0 >= tot0)) continue;
+                    if (cand == 1 && nx1 == 0 && nx0 < lead) continue;
+                    if ((cand ? jj1 : jj0) != 0 && !(cand ? open1 : open0)) {
+                        if (!mbar_probe(BAR(BAR_AREADY + cand), (cand ? stg1 : stg0) & 1u)) continue;
+                        if (cand) open1 = true; else open0 = true;
+                    }
                     s = cand;
                 }
                 if (s < 0) { __nanosleep(32); continue; }
                 RVQ_LAP(0)
-                const int ridx = it % RING;
-                mbar_wait(BAR(BAR_BEMPTY + ridx), (((uint32_t)(it / RING)) & 1u) ^ 1u);
+                RVQ_TL(0x100 | s)
+                // any free ring entry will do (an entry can be held for a long time by a tile requested ahead
+                // of its slot's operand rows)
+                int ridx = rnext;
+                while (!mbar_probe(BAR(BAR_BEMPTY + ridx), ((upar >> ridx) & 1u) ^ 1u)) ridx = ridx + 1 == RING ? 0 : ridx + 1;
+                const uint32_t rpar = (upar >> ridx) & 1u;
+                upar ^= 1u << ridx;
+                rnext = ridx + 1 == RING ? 0 : ridx + 1;
+                RVQ_TL(0x110 | s)
                 RVQ_LAP(1)
-                ring_meta[ridx] = (uint32_t)s;
-                const int i = s ? next1 : next0;
-                const int k = (i / NT) % K, j = i % NT;
-                mbar_arrive_expect_tx(BAR(BAR_BFULL + ridx), IMG);
-                bulk_g2s(base + SM_RING + ridx * IMG, P.img + ((size_t)k * NT + j) * IMG, IMG, BAR(BAR_BFULL + ridx));
-                if (s) ++next1; else ++next0;
+                const int nxs = s ? nx1 : nx0, iis = s ? ii1 : ii0;
+                if (elect_one()) {
+                    // message to the slot's MMA warp: which ring entry holds its next tile
+                    fifo[s * 4 + (nxs & 3)] = ((uint32_t)((nxs + 1) & 0xFFFF) << 16) | (rpar << 8) | (uint32_t)ridx;
+                    mbar_arrive_expect_tx(BAR(BAR_BFULL + ridx), IMG);
+                    bulk_g2s(base + SM_RING + ridx * IMG, P.img + (size_t)iis * IMG, IMG, BAR(BAR_BFULL + ridx));
+                }
+                __syncwarp();
+                if (s) {
+                    ++nx1;
+                    if (++ii1 == per_tile) ii1 = 0;
+                    if (++jj1 == NT) { jj1 = 0; ++stg1; open1 = false; }
+                } else {
+                    ++nx0;
+                    if (++ii0 == per_tile) ii0 = 0;
+                    if (++jj0 == NT) { jj0 = 0; ++stg0; open0 = false; }
+                }
                 last = s;
-                ++it;
             }
-        } else if (warp == 1) {
-            // ============================ MMA issuer (whole warp waits, one elected lane issues) ============================
-            const int total = (slot_tiles(P.ntiles, grid, cta, 0) + slot_tiles(P.ntiles, grid, cta, 1)) * per_tile;
-            int cnt0 = 0, cnt1 = 0;
-            const uint64_t adesc0 = desc_sw128(base + SM_A), bdesc0 = desc_sw128(base + SM_RING);
-            const uint64_t aaug0 = desc_interleaved(base + SM_A + 32768), baug0 = desc_interleaved(base + SM_RING + 32768);
-            for (int it = 0; it < total; ++it) {
-                const int ridx = it % RING;
+        } else if (warp <= NSLOT) {
+            // ============================ MMA issuer of slot warp-1 (whole warp waits, one elected lane issues) ======
+            const int s = warp - 1;
+            const int total = slot_tiles(P.ntiles, grid, cta, s) * per_tile;
+            const uint64_t adesc = desc_sw128(base + SM_A) + (uint64_t)(s * (IMG >> 4));
+            const uint64_t aaug = desc_interleaved(base + SM_A + 32768) + (uint64_t)(s * (IMG >> 4));
+            const uint64_t bdesc0 = desc_sw128(base + SM_RING), baug0 = desc_interleaved(base + SM_RING + 32768);
+            int j = 0;
+            uint32_t stage_par = 0;
+            for (int n = 0; n < total; ++n) {
                 RVQ_LAP(0)
-                mbar_wait(BAR(BAR_BFULL + ridx), ((uint32_t)(it / RING)) & 1u);
+                RVQ_TL(0x200)
+                uint32_t msg;
+                do { msg = fifo[s * 4 + (n & 3)]; } while ((msg >> 16) != (uint32_t)((n + 1) & 0xFFFF));
+                const int ridx = (int)(msg & 0xFFu);
+                mbar_wait(BAR(BAR_BFULL + ridx), (msg >> 8) & 1u);
+                RVQ_TL(0x210)
                 RVQ_LAP(1)
-                const int s = (int)ring_meta[ridx];
-                const int c = s ? cnt1 : cnt0;
-                if (c % NT == 0) mbar_wait(BAR(BAR_AREADY + s), (uint32_t)(c / NT) & 1u);
+                if (j == 0) mbar_wait(BAR(BAR_AREADY + s), stage_par);
                 RVQ_LAP(2)
-                const int buf = c & 1;
-                mbar_wait(BAR(BAR_ACCEMPTY + s * 2 + buf), (((uint32_t)(c >> 1)) & 1u) ^ 1u);
+                const int buf = n & 1;
+                mbar_wait(BAR(BAR_ACCEMPTY + s * 2 + buf), (((uint32_t)(n >> 1)) & 1u) ^ 1u);
                 RVQ_LAP(3)
+                RVQ_TL(0x220 | s)
                 tc_fence_after();
                 const uint32_t d = tmem + (uint32_t)(s * 256 + buf * 128);
                 // descriptors: only the 14-bit start address field changes (16-byte units)
-                const uint64_t a0 = adesc0 + (uint64_t)(s * (IMG >> 4)), b0 = bdesc0 + (uint64_t)(ridx * (IMG >> 4));
+                const uint64_t b0 = bdesc0 + (uint64_t)(ridx * (IMG >> 4));
                 if (elect_one()) {
 #pragma unroll
                     for (int kb = 0; kb < 2; ++kb)
 #pragma unroll
                         for (int ks = 0; ks < 4; ++ks)
-                            umma_f16(d, a0 + (uint64_t)(kb * 1024 + ks * 2), b0 + (uint64_t)(kb * 1024 + ks * 2), IDESC,
+                            umma_f16(d, adesc + (uint64_t)(kb * 1024 + ks * 2), b0 + (uint64_t)(kb * 1024 + ks * 2), IDESC,
                                      (kb | ks) ? 1u : 0u);
-                    umma_f16(d, aaug0 + (uint64_t)(s * (IMG >> 4)), baug0 + (uint64_t)(ridx * (IMG >> 4)), IDESC, 1u);
+                    umma_f16(d, aaug, baug0 + (uint64_t)(ridx * (IMG >> 4)), IDESC, 1u);
                     umma_commit(BAR(BAR_BEMPTY + ridx));
                     umma_commit(BAR(BAR_ACCFULL + s * 2 + buf));
                 }
                 __syncwarp();
-                if (s) ++cnt1; else ++cnt0;
+                RVQ_TL(0x230 | s)
+                if (++j == NT) { j = 0; stage_par ^= 1u; }
             }
         }
     } else {
@@ -563,6 +616,7 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
                 fence_proxy_async();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(BAR(BAR_AREADY + slot));
+                RVQ_TL(0x300 | k)
 
                 // ---- scan: this thread's frame = TMEM lane row_l.  A group = the 16 codes of one TMEM load.
                 // A group whose maximum is within 2*delta of the running maximum is remembered: its packed
@@ -612,8 +666,10 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
                 for (int j = 0; j < NT; ++j, ++items) {
                     const int buf = items & 1;
                     float ga[4], gb[4];
+                    RVQ_TL(0x310)
                     tmem_wait_ld();
                     tmem_ld64(tq + buf * 128 + 64, vb);
+                    RVQ_TL(0x320)
                     RVQ_LAP(3)
                     half_max(va, ga);
                     tmem_wait_ld();
@@ -637,9 +693,11 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
                         }
                     }
                     remember(vb, gb, j, 1);
+                    RVQ_TL(0x330 | (started ? 1 : 0))
                     RVQ_LAP(4)
                     if (j + 1 < NT && !started) {
                         mbar_wait(nbar, npar);
+                        RVQ_TL(0x340)
                         tc_fence_after();
                         tmem_ld64(tq + (buf ^ 1) * 128, va);
                     }
@@ -705,6 +763,7 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
                 }
                 __syncwarp();  // lists (written by lane = frame) are read by every lane in resolve_slow
                 RVQ_LAP(5)
+                RVQ_TL(0x350)
 
                 // ---- resolve, phase 2a: the frames with more than one candidate, exact fp32 in the canonical order
                 for (unsigned amb = __ballot_sync(0xffffffffu, ncand != 1); amb; amb &= amb - 1) {
@@ -739,6 +798,7 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
                 }
                 const int mycode = myidx;
                 RVQ_LAP(6)
+                RVQ_TL(0x360)
 
                 // ---- resolve, phase 2b: residual update and the next stage's operand row, four frames per
                 // iteration (independent dependency chains side by side), the winners' rows and the residuals
@@ -787,6 +847,7 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
                 if (n0 + lane < P.N) P.codes[(int64_t)k * P.N + n0 + lane] = (int64_t)mycode;
                 xx = xx_next;
                 __syncwarp();
+                RVQ_TL(0x370)
                 RVQ_LAP(7)
             }
         }
@@ -795,6 +856,7 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
         for (int i = 0; i < 8; ++i) P.dbg_time[warp * 8 + i] = tm[i];
     }
 #undef RVQ_LAP
+#undef RVQ_TL
 
     tc_fence_before();
     __syncthreads();
@@ -864,7 +926,11 @@ static int launch_tc(const float *x, const int64_t xs[3], int B, int T, const Rv
                 RVQ_EINVAL, "rvq_encode_f32: a 16-byte aligned workspace of rvq_encode_workspace_bytes() bytes is required");
     P.scratch = reinterpret_cast<float *>((char *)workspace + WS_HEADER);
     P.vals = reinterpret_cast<float *>((char *)workspace + WS_HEADER + WS_R_PER_CTA * grid);
+#ifdef RVQ_TIMELINE
+    if (false) {
+#else
     if (dbg_acc) {
+#endif
         RVQ_CUDA(cudaFuncSetAttribute(rvq_encode_tc_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_ALLOC));
         rvq_encode_tc_kernel<true, true><<<grid, THREADS, SM_ALLOC, stream>>>(P);
     } else if (dbg_info) {  // cycle counters only: the production code path plus clock reads

@@ -158,6 +158,21 @@ __device__ __forceinline__ float group_max8(const uint32_t *v) {
     m = max3(m, __uint_as_float(v[5]), __uint_as_float(v[6]));
     return fmaxf(m, __uint_as_float(v[7]));
 }
+// Predicated "remember this group": its 16 approximate scores to the L2 scratch, its packed list word to shared
+// memory.  Straight-line code: a branch per group costs far more than the predicated-off instructions.
+__device__ __forceinline__ void remember_store(bool on, float *gdst, const uint32_t *v, uint32_t sdst, uint32_t word) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %0, 0;\n\t"
+        "@p st.global.v4.b32 [%1], {%2, %3, %4, %5};\n\t"
+        "@p st.global.v4.b32 [%1+16], {%6, %7, %8, %9};\n\t"
+        "@p st.global.v4.b32 [%1+32], {%10, %11, %12, %13};\n\t"
+        "@p st.global.v4.b32 [%1+48], {%14, %15, %16, %17};\n\t"
+        "@p st.shared.b32 [%18], %19;\n\t}"
+        ::"r"((int)on), "l"(gdst), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]),
+        "r"(v[8]), "r"(v[9]), "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15]), "r"(sdst), "r"(word)
+        : "memory");
+}
 __device__ __forceinline__ void tmem_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 // K-major SWIZZLE_128B operand: rows of 128 bytes, 8-row groups 1024 bytes apart (SBO), version 1
@@ -635,6 +650,8 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
                 };
                 // remember the groups of one half that are within 2*delta of the maximum seen so far
                 // (which already includes this whole accumulator)
+                float *vals_row = vals + (size_t)row_l * 16;             // + cnt * TILE_M * 16
+                const uint32_t list_row = smem_u32(list + row_l);        // + cnt * TILE_M * 4
                 auto remember = [&](const uint32_t(&v)[64], const float(&gmx)[4], int j, int half) {
 #pragma unroll
                     for (int g = 0; g < 4; ++g) {
@@ -644,18 +661,11 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
                             for (int i = 0; i < 16; ++i)
                                 P.dbg_acc[(size_t)row_l * C + j * 128 + half * 64 + g * 16 + i] = __uint_as_float(vg[i]);
                         }
-                        if (gmx[g] >= thr) {
-                            if (cnt < LISTCAP) {
-                                list[cnt * TILE_M + row_l] =
-                                    (__float_as_uint(gmx[g]) & ~0x7FFu) | (uint32_t)(j * 8 + half * 4 + g);
-                                uint4 *dst = reinterpret_cast<uint4 *>(vals + ((size_t)cnt * TILE_M + row_l) * 16);
-                                dst[0] = make_uint4(vg[0], vg[1], vg[2], vg[3]);
-                                dst[1] = make_uint4(vg[4], vg[5], vg[6], vg[7]);
-                                dst[2] = make_uint4(vg[8], vg[9], vg[10], vg[11]);
-                                dst[3] = make_uint4(vg[12], vg[13], vg[14], vg[15]);
-                            }
-                            ++cnt;
-                        }
+                        const bool pass = gmx[g] >= thr;
+                        remember_store(pass && cnt < LISTCAP, vals_row + (size_t)cnt * (TILE_M * 16), vg,
+                                       list_row + (uint32_t)cnt * (TILE_M * 4),
+                                       (__float_as_uint(gmx[g]) & ~0x7FFu) | (uint32_t)(j * 8 + half * 4 + g));
+                        cnt += pass ? 1 : 0;
                     }
                 };
                 const uint32_t tq = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(slot * 256);

@@ -43,7 +43,7 @@ def run(B=64, T=1500):
     K = 4
     codes = torch.empty((K, B, T), dtype=torch.int64, device="cuda")
     info = torch.zeros((128 * 8 + 192,), device="cuda")
-    tl = torch.zeros((12, 4096, 2), dtype=torch.int64, device="cuda")
+    tl = torch.zeros((20, 4096, 2), dtype=torch.int64, device="cuda")
     ws_bytes = lib.rvq_encode_workspace_bytes(B, D, T, K, C, _lib.ALGO_TC)
     ws = torch.empty(ws_bytes, dtype=torch.uint8, device="cuda")
     for _ in range(3):
@@ -63,8 +63,8 @@ def run(B=64, T=1500):
 
 def digest(ev):
     import numpy as np
-    t0 = min(int(ev[w, 0, 1]) for w in range(12) if ev[w, 0, 0])
-    for w in (0, 1, 4, 8):
+    t0 = min(int(ev[w, 0, 1]) for w in range(ev.shape[0]) if ev[w, 0, 0])
+    for w in (0, 1, 4, 12):
         n = int((ev[w, :, 0] != 0).sum())
         print(f"warp {w}: {n} events, last at {int(ev[w, n - 1, 1]) - t0}")
     # MMA warp: per item wait for B, wait for accumulator, issue
@@ -88,7 +88,7 @@ def digest(ev):
     w = clk[1::2][: n // 2] - clk[0::2][: n // 2]
     print(f"producer: {n // 2} tiles, wait_b_empty mean {w.mean():.0f} sum {w.sum()}")
     # frame warp 4 (slot 0) and 8 (slot 1): per stage phases
-    for wp in (4, 8):
+    for wp in (4, 8, 12):
         e = ev[wp]
         n = int((e[:, 0] != 0).sum())
         tags, clk = e[:n, 0], e[:n, 1] - t0

@@ -725,19 +725,22 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
                 if (flags == 0 && cnt <= LISTCAP) {
                     const float keep = M - twodelta;
                     const float keep_packed = keep - 0.0009765625f * (fabsf(M) + twodelta);  // 11 mantissa bits were cleared
-                    // pass A (shared memory only): which remembered groups survive?  Up to 3 are examined here.
-                    int ne = 0, e0 = 0, e1 = 0, e2 = 0;
-                    uint32_t u0 = 0, u1 = 0, u2 = 0;
-                    for (int e = 0; e < cnt; ++e) {
+                    // pass A (shared memory only, straight-line: all LISTCAP words are read, those past cnt ignored):
+                    // which remembered groups survive?  Up to 3 are examined here.
+                    uint32_t sm_mask = 0;
+#pragma unroll
+                    for (int e = 0; e < LISTCAP; ++e) {
                         const uint32_t u = list[e * TILE_M + row_l];
-                        if (__uint_as_float(u & ~0x7FFu) >= keep_packed) {
-                            if (ne == 0) { e0 = e; u0 = u; }
-                            else if (ne == 1) { e1 = e; u1 = u; }
-                            else if (ne == 2) { e2 = e; u2 = u; }
-                            ++ne;
-                        }
+                        const bool ok = e < cnt && __uint_as_float(u & ~0x7FFu) >= keep_packed;
+                        sm_mask |= ok ? (1u << e) : 0u;
                     }
+                    const int ne = __popc(sm_mask);
                     if (ne >= 1 && ne <= 3) {
+                        const int e0 = __ffs(sm_mask) - 1;
+                        const uint32_t m1 = sm_mask & (sm_mask - 1u);
+                        const int e1 = m1 ? __ffs(m1) - 1 : e0;
+                        const uint32_t m2 = m1 & (m1 - 1u);
+                        const int e2 = m2 ? __ffs(m2) - 1 : e0;
                         // pass B: one round trip to the L2 scratch for all surviving groups
                         float4 t[3][4];
 #pragma unroll
@@ -745,29 +748,33 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
                             const int e = s3 == 0 ? e0 : (s3 == 1 ? e1 : e2);
                             const float4 *src = reinterpret_cast<const float4 *>(vals + ((size_t)e * TILE_M + row_l) * 16);
 #pragma unroll
-                            for (int qd = 0; qd < 4; ++qd)
-                                t[s3][qd] = s3 < ne ? src[qd] : make_float4(-CUDART_INF_F, -CUDART_INF_F, -CUDART_INF_F, -CUDART_INF_F);
+                            for (int qd = 0; qd < 4; ++qd) t[s3][qd] = src[qd];  // (a duplicate of group e0 when s3 >= ne)
                         }
-                        ncand = 0;
+                        const uint32_t u0 = list[e0 * TILE_M + row_l], u1 = list[e1 * TILE_M + row_l], u2 = list[e2 * TILE_M + row_l];
+                        // 16-bit masks of the codes within 2*delta of the maximum, one per surviving group
+                        uint32_t cm[3];
 #pragma unroll
                         for (int s3 = 0; s3 < 3; ++s3) {
-                            const int cbase = (int)((s3 == 0 ? u0 : (s3 == 1 ? u1 : u2)) & 0x7FFu) * 16;
+                            uint32_t mk = 0;
 #pragma unroll
                             for (int qd = 0; qd < 4; ++qd) {
-                                const float tv[4] = {t[s3][qd].x, t[s3][qd].y, t[s3][qd].z, t[s3][qd].w};
-#pragma unroll
-                                for (int i = 0; i < 4; ++i) {
-                                    if (tv[i] >= keep) {
-                                        const int col = cbase + qd * 4 + i;
-                                        if (ncand == 0) myidx = col;
-                                        else if (ncand == 1) c1 = col;
-                                        else if (ncand == 2) c2 = col;
-                                        else if (ncand == 3) c3 = col;
-                                        ++ncand;
-                                    }
-                                }
+                                mk |= t[s3][qd].x >= keep ? (1u << (qd * 4 + 0)) : 0u;
+                                mk |= t[s3][qd].y >= keep ? (1u << (qd * 4 + 1)) : 0u;
+                                mk |= t[s3][qd].z >= keep ? (1u << (qd * 4 + 2)) : 0u;
+                                mk |= t[s3][qd].w >= keep ? (1u << (qd * 4 + 3)) : 0u;
                             }
+                            cm[s3] = s3 < ne ? mk : 0u;
                         }
+                        unsigned long long mm = (unsigned long long)cm[0] | ((unsigned long long)cm[1] << 16) |
+                                                ((unsigned long long)cm[2] << 32);
+                        ncand = __popcll(mm);
+                        const int b0 = (int)(u0 & 0x7FFu) * 16, b1 = (int)(u1 & 0x7FFu) * 16, b2 = (int)(u2 & 0x7FFu) * 16;
+                        auto take = [&]() {  // lowest set position -> code index; clears it
+                            const int pos = mm ? __ffsll((long long)mm) - 1 : 0;
+                            mm &= mm - 1ull;
+                            return (pos < 16 ? b0 : (pos < 32 ? b1 : b2)) + (pos & 15);
+                        };
+                        myidx = take(); c1 = take(); c2 = take(); c3 = take();
                         if (ncand == 0 || ncand > 4) ncand = 99;  // 0 cannot happen (the maximum itself qualifies)
                     }
                 }
@@ -775,27 +782,46 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
                 RVQ_LAP(5)
                 RVQ_TL(0x350)
 
-                // ---- resolve, phase 2a: the frames with more than one candidate, exact fp32 in the canonical order
-                for (unsigned amb = __ballot_sync(0xffffffffu, ncand != 1); amb; amb &= amb - 1) {
+                // ---- resolve, phase 2a: the frames with more than one candidate, exact fp32 in the canonical order.
+                // Two frames per iteration where possible, so that their loads share one round trip to L2.
+                auto best_of = [&](const float4 &rf, float xf, int nc, int j0, int j1, int j2, int j3) {
+                    float bs = exact_score(rf, xf, Ek, cnk, j0, lane);
+                    int idx = j0;
+                    const float s1 = exact_score(rf, xf, Ek, cnk, j1, lane);
+                    if (rvq_better(s1, j1, bs, idx)) { bs = s1; idx = j1; }
+                    if (nc > 2) {
+                        const float s2 = exact_score(rf, xf, Ek, cnk, j2, lane);
+                        if (rvq_better(s2, j2, bs, idx)) { bs = s2; idx = j2; }
+                    }
+                    if (nc > 3) {
+                        const float s3 = exact_score(rf, xf, Ek, cnk, j3, lane);
+                        if (rvq_better(s3, j3, bs, idx)) { bs = s3; idx = j3; }
+                    }
+                    return idx;
+                };
+                for (unsigned amb = __ballot_sync(0xffffffffu, ncand != 1); amb;) {
                     const int f = __ffs(amb) - 1;
+                    amb &= amb - 1;
                     const int nc = __shfl_sync(0xffffffffu, ncand, f);
                     const float xf = __shfl_sync(0xffffffffu, xx, f);
                     const float4 rf = rs4[f * 32];
                     int idx;
                     if (nc <= 4) {
-                        const int k0 = __shfl_sync(0xffffffffu, myidx, f), k1 = __shfl_sync(0xffffffffu, c1, f);
-                        const int k2 = __shfl_sync(0xffffffffu, c2, f), k3 = __shfl_sync(0xffffffffu, c3, f);
-                        float bs = exact_score(rf, xf, Ek, cnk, k0, lane);
-                        idx = k0;
-                        const float s1 = exact_score(rf, xf, Ek, cnk, k1, lane);
-                        if (rvq_better(s1, k1, bs, idx)) { bs = s1; idx = k1; }
-                        if (nc > 2) {
-                            const float s2 = exact_score(rf, xf, Ek, cnk, k2, lane);
-                            if (rvq_better(s2, k2, bs, idx)) { bs = s2; idx = k2; }
-                        }
-                        if (nc > 3) {
-                            const float s3 = exact_score(rf, xf, Ek, cnk, k3, lane);
-                            if (rvq_better(s3, k3, bs, idx)) { bs = s3; idx = k3; }
+                        const int j0 = __shfl_sync(0xffffffffu, myidx, f), j1 = __shfl_sync(0xffffffffu, c1, f);
+                        const int j2 = __shfl_sync(0xffffffffu, c2, f), j3 = __shfl_sync(0xffffffffu, c3, f);
+                        const int g = amb ? __ffs(amb) - 1 : f;                 // the next ambiguous frame, if any
+                        const int ncg = __shfl_sync(0xffffffffu, ncand, g);
+                        if (amb && ncg <= 4) {
+                            amb &= amb - 1;
+                            const float xg = __shfl_sync(0xffffffffu, xx, g);
+                            const float4 rg = rs4[g * 32];
+                            const int i0 = __shfl_sync(0xffffffffu, myidx, g), i1 = __shfl_sync(0xffffffffu, c1, g);
+                            const int i2 = __shfl_sync(0xffffffffu, c2, g), i3 = __shfl_sync(0xffffffffu, c3, g);
+                            idx = best_of(rf, xf, nc, j0, j1, j2, j3);
+                            const int idg = best_of(rg, xg, ncg, i0, i1, i2, i3);
+                            if (lane == g) myidx = idg;
+                        } else {
+                            idx = best_of(rf, xf, nc, j0, j1, j2, j3);
                         }
                     } else {
                         const int cf = __shfl_sync(0xffffffffu, cnt, f);
@@ -810,13 +836,13 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
                 RVQ_LAP(6)
                 RVQ_TL(0x360)
 
-                // ---- resolve, phase 2b: residual update and the next stage's operand row, four frames per
-                // iteration (independent dependency chains side by side), the winners' rows and the residuals
-                // of the next four requested one iteration ahead
+                // ---- resolve, phase 2b: residual update and the next stage's operand row, eight frames per
+                // iteration: one round trip to L2 (winners' rows, residuals) per iteration, requested for the next
+                // eight as soon as the registers are free, so that it overlaps the operand conversion of these
                 const bool more = k + 1 < K;
                 float xx_next = 0.0f;
                 if (more) {
-                    constexpr int NB = 4;
+                    constexpr int NB = 8;
                     mt = P.meta[k + 1];
                     float4 w[NB], rf[NB];
 #pragma unroll
@@ -827,14 +853,6 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
                     }
 #pragma unroll 1
                     for (int f = 0; f < 32; f += NB) {
-                        float4 w_n[NB], rf_n[NB];
-#pragma unroll
-                        for (int t = 0; t < NB; ++t) {
-                            const int fn = min(f + NB + t, 31);
-                            const int id = __shfl_sync(0xffffffffu, myidx, fn);
-                            w_n[t] = __ldg(reinterpret_cast<const float4 *>(Ek + (size_t)id * 128) + lane);
-                            rf_n[t] = rs4[fn * 32];
-                        }
                         float4 rn[NB];
 #pragma unroll
                         for (int t = 0; t < NB; ++t) {
@@ -845,13 +863,19 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
                             rn[t].w = __fsub_rn(rf[t].w, w[t].w);
                             rs4[(f + t) * 32] = rn[t];
                         }
+                        if (f + NB < 32) {
+#pragma unroll
+                            for (int t = 0; t < NB; ++t) {
+                                const int id = __shfl_sync(0xffffffffu, myidx, f + NB + t);
+                                w[t] = __ldg(reinterpret_cast<const float4 *>(Ek + (size_t)id * 128) + lane);
+                                rf[t] = rs4[(f + NB + t) * 32];
+                            }
+                        }
 #pragma unroll
                         for (int t = 0; t < NB; ++t) {
                             const float xv = emit_row(A, q * 32 + f + t, lane, rn[t], mt);
                             if (lane == f + t) xx_next = xv;
                         }
-#pragma unroll
-                        for (int t = 0; t < NB; ++t) { w[t] = w_n[t]; rf[t] = rf_n[t]; }
                     }
                 }
                 if (n0 + lane < P.N) P.codes[(int64_t)k * P.N + n0 + lane] = (int64_t)mycode;

@@ -393,13 +393,10 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t bar0 = base + SM_BAR;
     auto BAR = [&](int i) { return bar0 + 8u * (uint32_t)i; };
-    // fifo[slot][4]: producer -> MMA warp of the slot, (sequence number << 16) | (ring parity << 8) | ring entry
-    volatile uint32_t *fifo = reinterpret_cast<volatile uint32_t *>(sm + SM_META + 32);
     volatile uint32_t *tmem_slot = reinterpret_cast<volatile uint32_t *>(sm + SM_META + 16);
 
-    if (threadIdx.x < NSLOT * 4) fifo[threadIdx.x] = 0u;
     if (threadIdx.x == 0) {
-        for (int i = 0; i < RING; ++i) { mbar_init(BAR(BAR_BFULL + i), 1); mbar_init(BAR(BAR_BEMPTY + i), 1); }
+        for (int i = 0; i < RING; ++i) { mbar_init(BAR(BAR_BFULL + i), 1); mbar_init(BAR(BAR_BEMPTY + i), NSLOT); }
         for (int i = 0; i < 4; ++i) { mbar_init(BAR(BAR_ACCFULL + i), 1); mbar_init(BAR(BAR_ACCEMPTY + i), 4); }
         for (int i = 0; i < NSLOT; ++i) mbar_init(BAR(BAR_AREADY + i), 4);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -448,106 +445,75 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
 
     if (warp < 4) {
         asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+        // The two slots of a CTA run in lock step: they are at the same codebook tile (stage k, tile j) at the
+        // same time, so that one copy of the tile serves both (the L2 -> shared memory stream of codebook
+        // tiles is what saturates first otherwise, and it slows every other L2 access of the kernel down).
+        const int rounds0 = slot_tiles(P.ntiles, grid, cta, 0), rounds1 = slot_tiles(P.ntiles, grid, cta, 1);
+        const int total = rounds0 * per_tile;  // codebook tiles this CTA streams; rounds1 <= rounds0
         if (warp == 0) {
             // ============================ producer (whole warp, one elected lane issues) ============================
-            // Per slot: how many codebook tiles were requested so far, where in the stage / the image the next
-            // one is, and whether the slot's operand rows of the current stage are known to be complete.  Tile 0
-            // of a stage is requested before they are (the MMA warp of the slot waits for them itself), so that
-            // the first accumulator of the stage does not pay for the copy.
-            // (scalars, not arrays: the slot index is a run-time value and arrays would live in local memory)
-            const int tot0 = slot_tiles(P.ntiles, grid, cta, 0) * per_tile, tot1 = slot_tiles(P.ntiles, grid, cta, 1) * per_tile;
-            int nx0 = 0, nx1 = 0, jj0 = 0, jj1 = 0, ii0 = 0, ii1 = 0;
-            uint32_t stg0 = 0, stg1 = 0;
-            bool open0 = false, open1 = false;
-            const int lead = min(NT / 2, tot0);  // slot 1 starts half a stage behind slot 0
-            int last = 1, rnext = 0;
-            uint32_t upar = 0;  // bit e: parity of the number of tiles ring entry e has held so far
-            while (nx0 < tot0 || nx1 < tot1) {
-                int s = -1;
-#pragma unroll
-                for (int attempt = 0; attempt < 2; ++attempt) {
-                    const int cand = attempt == 0 ? (last ^ 1) : last;
-                    if (s >= 0 || (cand ? nx1 >= tot1 : nx0 >= tot0)) continue;
-                    if (cand == 1 && nx1 == 0 && nx0 < lead) continue;
-                    if ((cand ? jj1 : jj0) != 0 && !(cand ? open1 : open0)) {
-                        if (!mbar_probe(BAR(BAR_AREADY + cand), (cand ? stg1 : stg0) & 1u)) continue;
-                        if (cand) open1 = true; else open0 = true;
-                    }
-                    s = cand;
-                }
-                if (s < 0) { __nanosleep(32); continue; }
+            int ridx = 0, ii = 0;
+            uint32_t rpar = 0;
+            for (int it = 0; it < total; ++it) {
                 RVQ_LAP(0)
-                RVQ_TL(0x100 | s)
-                // any free ring entry will do (an entry can be held for a long time by a tile requested ahead
-                // of its slot's operand rows)
-                int ridx = rnext;
-                while (!mbar_probe(BAR(BAR_BEMPTY + ridx), ((upar >> ridx) & 1u) ^ 1u)) ridx = ridx + 1 == RING ? 0 : ridx + 1;
-                const uint32_t rpar = (upar >> ridx) & 1u;
-                upar ^= 1u << ridx;
-                rnext = ridx + 1 == RING ? 0 : ridx + 1;
-                RVQ_TL(0x110 | s)
+                RVQ_TL(0x100)
+                mbar_wait(BAR(BAR_BEMPTY + ridx), rpar ^ 1u);
+                RVQ_TL(0x110)
                 RVQ_LAP(1)
-                const int nxs = s ? nx1 : nx0, iis = s ? ii1 : ii0;
                 if (elect_one()) {
-                    // message to the slot's MMA warp: which ring entry holds its next tile
-                    fifo[s * 4 + (nxs & 3)] = ((uint32_t)((nxs + 1) & 0xFFFF) << 16) | (rpar << 8) | (uint32_t)ridx;
                     mbar_arrive_expect_tx(BAR(BAR_BFULL + ridx), IMG);
-                    bulk_g2s(base + SM_RING + ridx * IMG, P.img + (size_t)iis * IMG, IMG, BAR(BAR_BFULL + ridx));
+                    bulk_g2s(base + SM_RING + ridx * IMG, P.img + (size_t)ii * IMG, IMG, BAR(BAR_BFULL + ridx));
                 }
                 __syncwarp();
-                if (s) {
-                    ++nx1;
-                    if (++ii1 == per_tile) ii1 = 0;
-                    if (++jj1 == NT) { jj1 = 0; ++stg1; open1 = false; }
-                } else {
-                    ++nx0;
-                    if (++ii0 == per_tile) ii0 = 0;
-                    if (++jj0 == NT) { jj0 = 0; ++stg0; open0 = false; }
-                }
-                last = s;
+                if (++ii == per_tile) ii = 0;
+                if (++ridx == RING) { ridx = 0; rpar ^= 1u; }
             }
         } else if (warp <= NSLOT) {
             // ============================ MMA issuer of slot warp-1 (whole warp waits, one elected lane issues) ======
             const int s = warp - 1;
-            const int total = slot_tiles(P.ntiles, grid, cta, s) * per_tile;
+            const int mine = (s ? rounds1 : rounds0) * per_tile;  // tiles this slot consumes; the rest it only releases
             const uint64_t adesc = desc_sw128(base + SM_A) + (uint64_t)(s * (IMG >> 4));
             const uint64_t aaug = desc_interleaved(base + SM_A + 32768) + (uint64_t)(s * (IMG >> 4));
             const uint64_t bdesc0 = desc_sw128(base + SM_RING), baug0 = desc_interleaved(base + SM_RING + 32768);
-            int j = 0;
-            uint32_t stage_par = 0;
+            int j = 0, ridx = 0;
+            uint32_t stage_par = 0, rpar = 0;
             for (int n = 0; n < total; ++n) {
                 RVQ_LAP(0)
                 RVQ_TL(0x200)
-                uint32_t msg;
-                do { msg = fifo[s * 4 + (n & 3)]; } while ((msg >> 16) != (uint32_t)((n + 1) & 0xFFFF));
-                const int ridx = (int)(msg & 0xFFu);
-                mbar_wait(BAR(BAR_BFULL + ridx), (msg >> 8) & 1u);
+                mbar_wait(BAR(BAR_BFULL + ridx), rpar);
                 RVQ_TL(0x210)
                 RVQ_LAP(1)
-                if (j == 0) mbar_wait(BAR(BAR_AREADY + s), stage_par);
-                RVQ_LAP(2)
-                const int buf = n & 1;
-                mbar_wait(BAR(BAR_ACCEMPTY + s * 2 + buf), (((uint32_t)(n >> 1)) & 1u) ^ 1u);
-                RVQ_LAP(3)
-                RVQ_TL(0x220 | s)
-                tc_fence_after();
-                const uint32_t d = tmem + (uint32_t)(s * 256 + buf * 128);
-                // descriptors: only the 14-bit start address field changes (16-byte units)
-                const uint64_t b0 = bdesc0 + (uint64_t)(ridx * (IMG >> 4));
-                if (elect_one()) {
+                if (n < mine) {
+                    if (j == 0) mbar_wait(BAR(BAR_AREADY + s), stage_par);
+                    RVQ_LAP(2)
+                    const int buf = n & 1;
+                    mbar_wait(BAR(BAR_ACCEMPTY + s * 2 + buf), (((uint32_t)(n >> 1)) & 1u) ^ 1u);
+                    RVQ_LAP(3)
+                    RVQ_TL(0x220 | s)
+                    tc_fence_after();
+                    const uint32_t d = tmem + (uint32_t)(s * 256 + buf * 128);
+                    // descriptors: only the 14-bit start address field changes (16-byte units)
+                    const uint64_t b0 = bdesc0 + (uint64_t)(ridx * (IMG >> 4));
+                    if (elect_one()) {
 #pragma unroll
-                    for (int kb = 0; kb < 2; ++kb)
+                        for (int kb = 0; kb < 2; ++kb)
 #pragma unroll
-                        for (int ks = 0; ks < 4; ++ks)
-                            umma_f16(d, adesc + (uint64_t)(kb * 1024 + ks * 2), b0 + (uint64_t)(kb * 1024 + ks * 2), IDESC,
-                                     (kb | ks) ? 1u : 0u);
-                    umma_f16(d, aaug, baug0 + (uint64_t)(ridx * (IMG >> 4)), IDESC, 1u);
-                    umma_commit(BAR(BAR_BEMPTY + ridx));
-                    umma_commit(BAR(BAR_ACCFULL + s * 2 + buf));
+                            for (int ks = 0; ks < 4; ++ks)
+                                umma_f16(d, adesc + (uint64_t)(kb * 1024 + ks * 2), b0 + (uint64_t)(kb * 1024 + ks * 2), IDESC,
+                                         (kb | ks) ? 1u : 0u);
+                        umma_f16(d, aaug, baug0 + (uint64_t)(ridx * (IMG >> 4)), IDESC, 1u);
+                        umma_commit(BAR(BAR_BEMPTY + ridx));
+                        umma_commit(BAR(BAR_ACCFULL + s * 2 + buf));
+                    }
+                    __syncwarp();
+                    RVQ_TL(0x230 | s)
+                    if (++j == NT) { j = 0; stage_par ^= 1u; }
+                } else {
+                    // this slot has no tile in the last round: only hand the ring entry back
+                    if (elect_one()) mbar_arrive(BAR(BAR_BEMPTY + ridx));
+                    __syncwarp();
                 }
-                __syncwarp();
-                RVQ_TL(0x230 | s)
-                if (++j == NT) { j = 0; stage_par ^= 1u; }
+                if (++ridx == RING) { ridx = 0; rpar ^= 1u; }
             }
         }
     } else {
@@ -577,9 +543,11 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
                 float *st = reinterpret_cast<float *>(A + q * 4096);
                 for (int pass = 0; pass < 4; ++pass) {
                     __syncwarp();
-#pragma unroll 8
-                    for (int dd = 0; dd < 32; ++dd)
-                        st[dd * 32 + (lane ^ dd)] = xoff >= 0 ? P.x[xoff + (int64_t)(pass * 32 + dd) * P.xs_d] : 0.0f;
+                    float xv[32];  // the 32 loads of a pass in flight together: x comes from HBM
+#pragma unroll
+                    for (int dd = 0; dd < 32; ++dd) xv[dd] = xoff >= 0 ? P.x[xoff + (int64_t)(pass * 32 + dd) * P.xs_d] : 0.0f;
+#pragma unroll
+                    for (int dd = 0; dd < 32; ++dd) st[dd * 32 + (lane ^ dd)] = xv[dd];
                     __syncwarp();
 #pragma unroll 8
                     for (int f = 0; f < 32; ++f) rs[f * 128 + pass * 32 + lane] = st[lane * 32 + (f ^ lane)];
@@ -718,6 +686,22 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
                     o[5] = (float)flags; o[6] = scale_acc; o[7] = __half2float(a_aug);
                 }
 
+                // The next tile of this slot comes from HBM: ask for it now (last stage: no residual update follows),
+                // so that the tile load finds it in L2.
+                if (k == K - 1 && tile + 2 * grid < P.ntiles) {
+                    const int64_t nn = n_l + (int64_t)2 * grid * TILE_M;
+                    if (nn < P.N) {
+                        const float *xn = P.x + (nn / P.T) * P.xs_b + (nn % P.T) * P.xs_t;
+                        if (P.xs_d == 1) {
+#pragma unroll
+                            for (int dd = 0; dd < 128; dd += 32) asm volatile("prefetch.global.L2 [%0];" ::"l"(xn + dd));
+                        } else {
+#pragma unroll 16
+                            for (int dd = 0; dd < 128; ++dd) asm volatile("prefetch.global.L2 [%0];" ::"l"(xn + (int64_t)dd * P.xs_d));
+                        }
+                    }
+                }
+
                 // ---- resolve, phase 1 (lane = frame): the codes whose approximate score is within 2*delta of
                 // the maximum are the only ones that can win.  Exactly one such code (the common case): it is
                 // the winner, no exact arithmetic needed.  2..4: re-scored exactly below.  Otherwise resolve_slow.
@@ -799,6 +783,51 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
                     }
                     return idx;
                 };
+                // Exactly two candidates (nearly all ambiguous frames): four frames = eight codes per iteration, all
+                // their rows requested together (one round trip to L2), the eight canonical sums by one transposed
+                // butterfly.  With fewer than four frames left the last one is simply repeated.
+                for (unsigned two = __ballot_sync(0xffffffffu, ncand == 2); two;) {
+                    int fr[4], jj[8];
+                    float xf[4];
+                    float4 rfv[4], rows[8];
+#pragma unroll
+                    for (int t = 0; t < 4; ++t) {
+                        fr[t] = two ? __ffs(two) - 1 : fr[t ? t - 1 : 0];
+                        two &= two - 1u;  // (0 stays 0)
+                        xf[t] = __shfl_sync(0xffffffffu, xx, fr[t]);
+                        jj[2 * t] = __shfl_sync(0xffffffffu, myidx, fr[t]);
+                        jj[2 * t + 1] = __shfl_sync(0xffffffffu, c1, fr[t]);
+                        rfv[t] = rs4[fr[t] * 32];
+                        rows[2 * t] = __ldg(reinterpret_cast<const float4 *>(Ek + (size_t)jj[2 * t] * 128) + lane);
+                        rows[2 * t + 1] = __ldg(reinterpret_cast<const float4 *>(Ek + (size_t)jj[2 * t + 1] * 128) + lane);
+                    }
+                    float pc[8];
+#pragma unroll
+                    for (int c = 0; c < 8; ++c) {
+                        const float4 &r = rfv[c >> 1];
+                        float t = __fmaf_rn(r.x, rows[c].x, 0.0f);
+                        t = __fmaf_rn(r.y, rows[c].y, t);
+                        t = __fmaf_rn(r.z, rows[c].z, t);
+                        pc[c] = __fmaf_rn(r.w, rows[c].w, t);
+                    }
+                    const float dot = transposed_butterfly8(pc, lane);  // lane l: column (l >> 2) & 7
+                    const int col = (lane >> 2) & 7;
+                    int jc = jj[0];
+                    float xc = xf[0];
+#pragma unroll
+                    for (int c = 1; c < 8; ++c) {
+                        if (col == c) { jc = jj[c]; xc = xf[c >> 1]; }
+                    }
+                    const float sc = rvq_score(xc, dot, __ldg(cnk + jc));
+                    const float so = __shfl_xor_sync(0xffffffffu, sc, 4);  // the frame's other candidate
+                    const int jo = __shfl_xor_sync(0xffffffffu, jc, 4);
+                    const int win = rvq_better(so, jo, sc, jc) ? jo : jc;
+#pragma unroll
+                    for (int t = 0; t < 4; ++t) {
+                        const int wt = __shfl_sync(0xffffffffu, win, 8 * t);
+                        if (lane == fr[t]) { myidx = wt; ncand = 1; }
+                    }
+                }
                 for (unsigned amb = __ballot_sync(0xffffffffu, ncand != 1); amb;) {
                     const int f = __ffs(amb) - 1;
                     amb &= amb - 1;

@@ -541,13 +541,19 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
                 // lane = frame reads (coalesced when T is the contiguous axis), transposed 32 dims at a
                 // time through this warp's own 4 KB of the A tile into the scratch rows
                 float *st = reinterpret_cast<float *>(A + q * 4096);
+                float xv[32];  // the 32 loads of a pass in flight together, one pass ahead of the transposition
+#pragma unroll
+                for (int dd = 0; dd < 32; ++dd) xv[dd] = xoff >= 0 ? P.x[xoff + (int64_t)dd * P.xs_d] : 0.0f;
+#pragma unroll 1
                 for (int pass = 0; pass < 4; ++pass) {
                     __syncwarp();
-                    float xv[32];  // the 32 loads of a pass in flight together: x comes from HBM
-#pragma unroll
-                    for (int dd = 0; dd < 32; ++dd) xv[dd] = xoff >= 0 ? P.x[xoff + (int64_t)(pass * 32 + dd) * P.xs_d] : 0.0f;
 #pragma unroll
                     for (int dd = 0; dd < 32; ++dd) st[dd * 32 + (lane ^ dd)] = xv[dd];
+                    if (pass < 3) {
+#pragma unroll
+                        for (int dd = 0; dd < 32; ++dd)
+                            xv[dd] = xoff >= 0 ? P.x[xoff + (int64_t)((pass + 1) * 32 + dd) * P.xs_d] : 0.0f;
+                    }
                     __syncwarp();
 #pragma unroll 8
                     for (int f = 0; f < 32; ++f) rs[f * 128 + pass * 32 + lane] = st[lane * 32 + (f ^ lane)];
@@ -558,22 +564,36 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
             // ---- stage 0 operand rows; lane f keeps ||r_f||^2
             RvqStageMeta mt = P.meta[0];
             float xx = 0.0f;
-            for (int f0 = 0; f0 < 32; f0 += 4) {
-                float4 rf[4];
-#pragma unroll
-                for (int t = 0; t < 4; ++t) {  // four independent loads in flight
+            {
+                // eight frames per iteration, the next eight requested before these are converted
+                constexpr int NB = 8;
+                auto fetch = [&](int f) {
                     if (direct) {
-                        const int64_t o = __shfl_sync(0xffffffffu, xoff, f0 + t);
-                        rf[t] = o >= 0 ? *(reinterpret_cast<const float4 *>(P.x + o) + lane) : make_float4(0.f, 0.f, 0.f, 0.f);
-                    } else {
-                        rf[t] = rs4[(f0 + t) * 32];
+                        const int64_t o = __shfl_sync(0xffffffffu, xoff, f);
+                        return o >= 0 ? *(reinterpret_cast<const float4 *>(P.x + o) + lane) : make_float4(0.f, 0.f, 0.f, 0.f);
                     }
-                }
+                    return rs4[f * 32];
+                };
+                float4 rf[NB];
 #pragma unroll
-                for (int t = 0; t < 4; ++t) {
-                    if (direct) rs4[(f0 + t) * 32] = rf[t];
-                    const float xv = emit_row(A, q * 32 + f0 + t, lane, rf[t], mt);
-                    if (lane == f0 + t) xx = xv;
+                for (int t = 0; t < NB; ++t) rf[t] = fetch(t);
+#pragma unroll 1
+                for (int f0 = 0; f0 < 32; f0 += NB) {
+                    float4 cur[NB];
+#pragma unroll
+                    for (int t = 0; t < NB; ++t) {
+                        cur[t] = rf[t];
+                        if (direct) rs4[(f0 + t) * 32] = cur[t];
+                    }
+                    if (f0 + NB < 32) {
+#pragma unroll
+                        for (int t = 0; t < NB; ++t) rf[t] = fetch(f0 + NB + t);
+                    }
+#pragma unroll
+                    for (int t = 0; t < NB; ++t) {
+                        const float xv = emit_row(A, q * 32 + f0 + t, lane, cur[t], mt);
+                        if (lane == f0 + t) xx = xv;
+                    }
                 }
             }
             RVQ_LAP(1)

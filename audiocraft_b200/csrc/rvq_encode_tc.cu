@@ -885,45 +885,50 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
                 RVQ_LAP(6)
                 RVQ_TL(0x360)
 
-                // ---- resolve, phase 2b: residual update and the next stage's operand row, eight frames per
-                // iteration: one round trip to L2 (winners' rows, residuals) per iteration, requested for the next
-                // eight as soon as the registers are free, so that it overlaps the operand conversion of these
+                // ---- resolve, phase 2b: residual update and the next stage's operand row.  Batches of four frames;
+                // the winners' rows and the residuals of three batches are in flight (an L2 round trip lasts about as
+                // long as three batches take to convert), in four register sets addressed statically (fully unrolled).
                 const bool more = k + 1 < K;
                 float xx_next = 0.0f;
                 if (more) {
-                    constexpr int NB = 8;
+                    constexpr int NB = 4, NBATCH = 32 / NB, DEPTH = 3;
                     mt = P.meta[k + 1];
-                    float4 w[NB], rf[NB];
+                    float4 w[DEPTH + 1][NB], rf[DEPTH + 1][NB];
 #pragma unroll
-                    for (int t = 0; t < NB; ++t) {
-                        const int id = __shfl_sync(0xffffffffu, myidx, t);
-                        w[t] = __ldg(reinterpret_cast<const float4 *>(Ek + (size_t)id * 128) + lane);
-                        rf[t] = rs4[t * 32];
+                    for (int b = 0; b < DEPTH; ++b) {
+#pragma unroll
+                        for (int t = 0; t < NB; ++t) {
+                            const int id = __shfl_sync(0xffffffffu, myidx, b * NB + t);
+                            w[b][t] = __ldg(reinterpret_cast<const float4 *>(Ek + (size_t)id * 128) + lane);
+                            rf[b][t] = rs4[(b * NB + t) * 32];
+                        }
                     }
-#pragma unroll 1
-                    for (int f = 0; f < 32; f += NB) {
+#pragma unroll
+                    for (int b = 0; b < NBATCH; ++b) {
+                        const int set = b % (DEPTH + 1);
+                        if (b + DEPTH < NBATCH) {
+                            const int sn = (b + DEPTH) % (DEPTH + 1);
+#pragma unroll
+                            for (int t = 0; t < NB; ++t) {
+                                const int id = __shfl_sync(0xffffffffu, myidx, (b + DEPTH) * NB + t);
+                                w[sn][t] = __ldg(reinterpret_cast<const float4 *>(Ek + (size_t)id * 128) + lane);
+                                rf[sn][t] = rs4[((b + DEPTH) * NB + t) * 32];
+                            }
+                        }
                         float4 rn[NB];
 #pragma unroll
                         for (int t = 0; t < NB; ++t) {
                             // residual = residual - quantized (core_vq.py:394)
-                            rn[t].x = __fsub_rn(rf[t].x, w[t].x);
-                            rn[t].y = __fsub_rn(rf[t].y, w[t].y);
-                            rn[t].z = __fsub_rn(rf[t].z, w[t].z);
-                            rn[t].w = __fsub_rn(rf[t].w, w[t].w);
-                            rs4[(f + t) * 32] = rn[t];
-                        }
-                        if (f + NB < 32) {
-#pragma unroll
-                            for (int t = 0; t < NB; ++t) {
-                                const int id = __shfl_sync(0xffffffffu, myidx, f + NB + t);
-                                w[t] = __ldg(reinterpret_cast<const float4 *>(Ek + (size_t)id * 128) + lane);
-                                rf[t] = rs4[(f + NB + t) * 32];
-                            }
+                            rn[t].x = __fsub_rn(rf[set][t].x, w[set][t].x);
+                            rn[t].y = __fsub_rn(rf[set][t].y, w[set][t].y);
+                            rn[t].z = __fsub_rn(rf[set][t].z, w[set][t].z);
+                            rn[t].w = __fsub_rn(rf[set][t].w, w[set][t].w);
+                            rs4[(b * NB + t) * 32] = rn[t];
                         }
 #pragma unroll
                         for (int t = 0; t < NB; ++t) {
-                            const float xv = emit_row(A, q * 32 + f + t, lane, rn[t], mt);
-                            if (lane == f + t) xx_next = xv;
+                            const float xv = emit_row(A, q * 32 + b * NB + t, lane, rn[t], mt);
+                            if (lane == b * NB + t) xx_next = xv;
                         }
                     }
                 }

@@ -28,6 +28,7 @@
 #include <math_constants.h>
 
 #include <mutex>
+#include <type_traits>
 
 #include "rvq_common.cuh"
 
@@ -730,7 +731,7 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
                     const float keep = M - twodelta;
                     const float keep_packed = keep - 0.0009765625f * (fabsf(M) + twodelta);  // 11 mantissa bits were cleared
                     // pass A (shared memory only, straight-line: all LISTCAP words are read, those past cnt ignored):
-                    // which remembered groups survive?  Up to 3 are examined here.
+                    // which remembered groups survive?  Up to 4 are examined here.
                     uint32_t sm_mask = 0;
 #pragma unroll
                     for (int e = 0; e < LISTCAP; ++e) {
@@ -739,44 +740,45 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
                         sm_mask |= ok ? (1u << e) : 0u;
                     }
                     const int ne = __popc(sm_mask);
-                    if (ne >= 1 && ne <= 3) {
-                        const int e0 = __ffs(sm_mask) - 1;
-                        const uint32_t m1 = sm_mask & (sm_mask - 1u);
-                        const int e1 = m1 ? __ffs(m1) - 1 : e0;
-                        const uint32_t m2 = m1 & (m1 - 1u);
-                        const int e2 = m2 ? __ffs(m2) - 1 : e0;
-                        // pass B: one round trip to the L2 scratch for all surviving groups
-                        float4 t[3][4];
+                    if (ne >= 1 && ne <= 4) {
+                        int es[4];
+                        uint32_t mrest = sm_mask;
 #pragma unroll
-                        for (int s3 = 0; s3 < 3; ++s3) {
-                            const int e = s3 == 0 ? e0 : (s3 == 1 ? e1 : e2);
-                            const float4 *src = reinterpret_cast<const float4 *>(vals + ((size_t)e * TILE_M + row_l) * 16);
-#pragma unroll
-                            for (int qd = 0; qd < 4; ++qd) t[s3][qd] = src[qd];  // (a duplicate of group e0 when s3 >= ne)
+                        for (int s4 = 0; s4 < 4; ++s4) {
+                            es[s4] = mrest ? __ffs(mrest) - 1 : es[0];
+                            mrest &= mrest - 1u;  // (0 stays 0)
                         }
-                        const uint32_t u0 = list[e0 * TILE_M + row_l], u1 = list[e1 * TILE_M + row_l], u2 = list[e2 * TILE_M + row_l];
-                        // 16-bit masks of the codes within 2*delta of the maximum, one per surviving group
-                        uint32_t cm[3];
+                        // pass B: one round trip to the L2 scratch for all surviving groups
+                        float4 t[4][4];
+                        uint32_t us[4];
 #pragma unroll
-                        for (int s3 = 0; s3 < 3; ++s3) {
+                        for (int s4 = 0; s4 < 4; ++s4) {
+                            const float4 *src = reinterpret_cast<const float4 *>(vals + ((size_t)es[s4] * TILE_M + row_l) * 16);
+#pragma unroll
+                            for (int qd = 0; qd < 4; ++qd)
+                                t[s4][qd] = s4 < ne ? src[qd] : make_float4(-CUDART_INF_F, -CUDART_INF_F, -CUDART_INF_F, -CUDART_INF_F);
+                            us[s4] = list[es[s4] * TILE_M + row_l];
+                        }
+                        // 16-bit masks of the codes within 2*delta of the maximum, one per surviving group
+                        unsigned long long mm = 0ull;
+#pragma unroll
+                        for (int s4 = 0; s4 < 4; ++s4) {
                             uint32_t mk = 0;
 #pragma unroll
                             for (int qd = 0; qd < 4; ++qd) {
-                                mk |= t[s3][qd].x >= keep ? (1u << (qd * 4 + 0)) : 0u;
-                                mk |= t[s3][qd].y >= keep ? (1u << (qd * 4 + 1)) : 0u;
-                                mk |= t[s3][qd].z >= keep ? (1u << (qd * 4 + 2)) : 0u;
-                                mk |= t[s3][qd].w >= keep ? (1u << (qd * 4 + 3)) : 0u;
+                                mk |= t[s4][qd].x >= keep ? (1u << (qd * 4 + 0)) : 0u;
+                                mk |= t[s4][qd].y >= keep ? (1u << (qd * 4 + 1)) : 0u;
+                                mk |= t[s4][qd].z >= keep ? (1u << (qd * 4 + 2)) : 0u;
+                                mk |= t[s4][qd].w >= keep ? (1u << (qd * 4 + 3)) : 0u;
                             }
-                            cm[s3] = s3 < ne ? mk : 0u;
+                            mm |= (unsigned long long)(s4 < ne ? mk : 0u) << (16 * s4);
                         }
-                        unsigned long long mm = (unsigned long long)cm[0] | ((unsigned long long)cm[1] << 16) |
-                                                ((unsigned long long)cm[2] << 32);
                         ncand = __popcll(mm);
-                        const int b0 = (int)(u0 & 0x7FFu) * 16, b1 = (int)(u1 & 0x7FFu) * 16, b2 = (int)(u2 & 0x7FFu) * 16;
                         auto take = [&]() {  // lowest set position -> code index; clears it
                             const int pos = mm ? __ffsll((long long)mm) - 1 : 0;
                             mm &= mm - 1ull;
-                            return (pos < 16 ? b0 : (pos < 32 ? b1 : b2)) + (pos & 15);
+                            const uint32_t u = pos < 16 ? us[0] : (pos < 32 ? us[1] : (pos < 48 ? us[2] : us[3]));
+                            return (int)(u & 0x7FFu) * 16 + (pos & 15);
                         };
                         myidx = take(); c1 = take(); c2 = take(); c3 = take();
                         if (ncand == 0 || ncand > 4) ncand = 99;  // 0 cannot happen (the maximum itself qualifies)
@@ -785,6 +787,13 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
                 __syncwarp();  // lists (written by lane = frame) are read by every lane in resolve_slow
                 RVQ_LAP(5)
                 RVQ_TL(0x350)
+#ifdef RVQ_TIMELINE
+                if (P.dbg_acc && n0 + lane < P.N) {  // histogram of candidate counts over all frames (after the event area)
+                    unsigned long long *hist = reinterpret_cast<unsigned long long *>(P.dbg_acc) + 12 * 4096 * 2;
+                    atomicAdd(hist + k * 8 + (ncand > 4 ? 5 : ncand), 1ull);
+                    atomicAdd(hist + 32 + k * 8 + min(cnt, 17) / 3, 1ull);
+                }
+#endif
 
                 // ---- resolve, phase 2a: the frames with more than one candidate, exact fp32 in the canonical order.
                 // Two frames per iteration where possible, so that their loads share one round trip to L2.
@@ -803,51 +812,68 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
                     }
                     return idx;
                 };
-                // Exactly two candidates (nearly all ambiguous frames): four frames = eight codes per iteration, all
-                // their rows requested together (one round trip to L2), the eight canonical sums by one transposed
-                // butterfly.  With fewer than four frames left the last one is simply repeated.
-                for (unsigned two = __ballot_sync(0xffffffffu, ncand == 2); two;) {
-                    int fr[4], jj[8];
-                    float xf[4];
-                    float4 rfv[4], rows[8];
+                // Two candidates (nearly all ambiguous frames): four frames = eight codes per iteration; three or four
+                // candidates: two frames per iteration.  All rows of an iteration are requested together (one round
+                // trip to L2), the eight canonical sums come from one transposed butterfly.  With fewer frames left
+                // than fit, the last one is repeated; a frame with three candidates scores its unused fourth slot too
+                // (a valid code that cannot win: its approximate score is more than 2*delta below the maximum).
+                auto rescore_batches = [&](unsigned todo, auto cpf_tag) {
+                    constexpr int CPF = decltype(cpf_tag)::value, FPI = 8 / CPF;
+                    while (todo) {
+                        int fr[FPI], jj[8];
+                        float xf[FPI];
+                        float4 rfv[FPI], rows[8];
 #pragma unroll
-                    for (int t = 0; t < 4; ++t) {
-                        fr[t] = two ? __ffs(two) - 1 : fr[t ? t - 1 : 0];
-                        two &= two - 1u;  // (0 stays 0)
-                        xf[t] = __shfl_sync(0xffffffffu, xx, fr[t]);
-                        jj[2 * t] = __shfl_sync(0xffffffffu, myidx, fr[t]);
-                        jj[2 * t + 1] = __shfl_sync(0xffffffffu, c1, fr[t]);
-                        rfv[t] = rs4[fr[t] * 32];
-                        rows[2 * t] = __ldg(reinterpret_cast<const float4 *>(Ek + (size_t)jj[2 * t] * 128) + lane);
-                        rows[2 * t + 1] = __ldg(reinterpret_cast<const float4 *>(Ek + (size_t)jj[2 * t + 1] * 128) + lane);
-                    }
-                    float pc[8];
+                        for (int t = 0; t < FPI; ++t) {
+                            fr[t] = todo ? __ffs(todo) - 1 : fr[t ? t - 1 : 0];
+                            todo &= todo - 1u;  // (0 stays 0)
+                            xf[t] = __shfl_sync(0xffffffffu, xx, fr[t]);
+                            jj[t * CPF] = __shfl_sync(0xffffffffu, myidx, fr[t]);
+                            jj[t * CPF + 1] = __shfl_sync(0xffffffffu, c1, fr[t]);
+                            if (CPF == 4) {
+                                jj[t * CPF + 2] = __shfl_sync(0xffffffffu, c2, fr[t]);
+                                jj[t * CPF + 3] = __shfl_sync(0xffffffffu, c3, fr[t]);
+                            }
+                            rfv[t] = rs4[fr[t] * 32];
 #pragma unroll
-                    for (int c = 0; c < 8; ++c) {
-                        const float4 &r = rfv[c >> 1];
-                        float t = __fmaf_rn(r.x, rows[c].x, 0.0f);
-                        t = __fmaf_rn(r.y, rows[c].y, t);
-                        t = __fmaf_rn(r.z, rows[c].z, t);
-                        pc[c] = __fmaf_rn(r.w, rows[c].w, t);
-                    }
-                    const float dot = transposed_butterfly8(pc, lane);  // lane l: column (l >> 2) & 7
-                    const int col = (lane >> 2) & 7;
-                    int jc = jj[0];
-                    float xc = xf[0];
+                            for (int i = 0; i < CPF; ++i)
+                                rows[t * CPF + i] = __ldg(reinterpret_cast<const float4 *>(Ek + (size_t)jj[t * CPF + i] * 128) + lane);
+                        }
+                        float pc[8];
 #pragma unroll
-                    for (int c = 1; c < 8; ++c) {
-                        if (col == c) { jc = jj[c]; xc = xf[c >> 1]; }
-                    }
-                    const float sc = rvq_score(xc, dot, __ldg(cnk + jc));
-                    const float so = __shfl_xor_sync(0xffffffffu, sc, 4);  // the frame's other candidate
-                    const int jo = __shfl_xor_sync(0xffffffffu, jc, 4);
-                    const int win = rvq_better(so, jo, sc, jc) ? jo : jc;
+                        for (int c = 0; c < 8; ++c) {
+                            const float4 &r = rfv[c / CPF];
+                            float t = __fmaf_rn(r.x, rows[c].x, 0.0f);
+                            t = __fmaf_rn(r.y, rows[c].y, t);
+                            t = __fmaf_rn(r.z, rows[c].z, t);
+                            pc[c] = __fmaf_rn(r.w, rows[c].w, t);
+                        }
+                        const float dot = transposed_butterfly8(pc, lane);  // lane l: column (l >> 2) & 7
+                        const int col = (lane >> 2) & 7;
+                        int jc = jj[0];
+                        float xc = xf[0];
 #pragma unroll
-                    for (int t = 0; t < 4; ++t) {
-                        const int wt = __shfl_sync(0xffffffffu, win, 8 * t);
-                        if (lane == fr[t]) { myidx = wt; ncand = 1; }
+                        for (int c = 1; c < 8; ++c) {
+                            if (col == c) { jc = jj[c]; xc = xf[c / CPF]; }
+                        }
+                        float sc = rvq_score(xc, dot, __ldg(cnk + jc));
+                        // best of the frame's CPF columns (4 lanes per column): a symmetric exchange, so every lane
+                        // of the frame's group ends with the same winner
+#pragma unroll
+                        for (int off = 4; off < 4 * CPF; off <<= 1) {
+                            const float so = __shfl_xor_sync(0xffffffffu, sc, off);
+                            const int jo = __shfl_xor_sync(0xffffffffu, jc, off);
+                            if (rvq_better(so, jo, sc, jc)) { sc = so; jc = jo; }
+                        }
+#pragma unroll
+                        for (int t = 0; t < FPI; ++t) {
+                            const int wt = __shfl_sync(0xffffffffu, jc, 4 * CPF * t);
+                            if (lane == fr[t]) { myidx = wt; ncand = 1; }
+                        }
                     }
-                }
+                };
+                rescore_batches(__ballot_sync(0xffffffffu, ncand == 2), std::integral_constant<int, 2>());
+                rescore_batches(__ballot_sync(0xffffffffu, ncand == 3 || ncand == 4), std::integral_constant<int, 4>());
                 for (unsigned amb = __ballot_sync(0xffffffffu, ncand != 1); amb;) {
                     const int f = __ffs(amb) - 1;
                     amb &= amb - 1;

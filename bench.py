@@ -338,7 +338,7 @@ def run_gpu_arm(args, rank: int, world: int, local_rank: int):
     achieved_tf = enc_flops / (enc_ms * 1e-3) / 1e12
     traffic = None
     try:  # DRAM bytes per launch of the encode kernel from the committed ncu --set full capture (profiles/)
-        with open(os.path.join(ROOT, "profiles", "r1_traffic.json")) as f:
+        with open(os.path.join(ROOT, "profiles", "r2_traffic.json")) as f:
             traffic = json.load(f).get("rvq_encode_tc_kernel_config2_bytes")
     except Exception:
         pass

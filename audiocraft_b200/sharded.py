@@ -94,6 +94,26 @@ class ShardedRVQ:
         full = torch.cat(parts, dim=1 if axis == 0 else 2).to(torch.int64)  # [K, B, T]
         return full.transpose(0, 1)
 
+    def gather_codes_async(self, codes_local: torch.Tensor, global_shape: tp.Tuple[int, int, int]):
+        """`gather_codes` on a side stream: returns (codes [B, K, T], event).  Nothing in the encode / decode of
+        the next batch depends on the gathered codes, so the all-gather (and the int16 <-> int64 conversions around
+        it) overlaps that work; a consumer calls `torch.cuda.current_stream().wait_event(event)` first."""
+        if self.world == 1:
+            ev = torch.cuda.Event()
+            ev.record()
+            return codes_local, ev
+        dev = codes_local.device
+        if getattr(self, "_gather_stream", None) is None:
+            self._gather_stream = torch.cuda.Stream(dev)
+        gs = self._gather_stream
+        gs.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(gs):
+            full = self.gather_codes(codes_local, global_shape)
+            codes_local.record_stream(gs)
+            ev = torch.cuda.Event()
+            ev.record(gs)
+        return full, ev
+
     # ---- whole-job calls ----------------------------------------------------------------------
     def encode(self, x_global_or_local: torch.Tensor, global_shape: tp.Optional[tp.Tuple[int, int, int]] = None,
                already_local: bool = False) -> torch.Tensor:

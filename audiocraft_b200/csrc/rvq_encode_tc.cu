@@ -127,6 +127,19 @@ __device__ __forceinline__ void umma_f16(uint32_t d_tmem, uint64_t adesc, uint64
         "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc)
         : "memory");
 }
+// the same with the descriptors as (low, high) words: only the low word (start address field) changes from MMA
+// to MMA, so the caller's arithmetic stays 32-bit
+__device__ __forceinline__ void umma_f16_lh(uint32_t d_tmem, uint32_t alo, uint32_t ahi, uint32_t blo, uint32_t bhi,
+                                            uint32_t idesc, uint32_t acc) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\t"
+        "setp.ne.b32 p, %6, 0;\n\t"
+        "mov.b64 da, {%1, %2};\n\t"
+        "mov.b64 db, {%3, %4};\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %5, p;\n\t}" ::"r"(d_tmem),
+        "r"(alo), "r"(ahi), "r"(blo), "r"(bhi), "r"(idesc), "r"(acc)
+        : "memory");
+}
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
@@ -493,16 +506,18 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
                     RVQ_TL(0x220 | s)
                     tc_fence_after();
                     const uint32_t d = tmem + (uint32_t)(s * 256 + buf * 128);
-                    // descriptors: only the 14-bit start address field changes (16-byte units)
-                    const uint64_t b0 = bdesc0 + (uint64_t)(ridx * (IMG >> 4));
+                    // descriptors: only the 14-bit start address field (low word, 16-byte units) changes
+                    const uint32_t blo = (uint32_t)bdesc0 + (uint32_t)(ridx * (IMG >> 4));
+                    const uint32_t bauglo = (uint32_t)baug0 + (uint32_t)(ridx * (IMG >> 4));
                     if (elect_one()) {
 #pragma unroll
                         for (int kb = 0; kb < 2; ++kb)
 #pragma unroll
                             for (int ks = 0; ks < 4; ++ks)
-                                umma_f16(d, adesc + (uint64_t)(kb * 1024 + ks * 2), b0 + (uint64_t)(kb * 1024 + ks * 2), IDESC,
-                                         (kb | ks) ? 1u : 0u);
-                        umma_f16(d, aaug, baug0 + (uint64_t)(ridx * (IMG >> 4)), IDESC, 1u);
+                                umma_f16_lh(d, (uint32_t)adesc + (uint32_t)(kb * 1024 + ks * 2), (uint32_t)(adesc >> 32),
+                                            blo + (uint32_t)(kb * 1024 + ks * 2), (uint32_t)(bdesc0 >> 32), IDESC,
+                                            (kb | ks) ? 1u : 0u);
+                        umma_f16_lh(d, (uint32_t)aaug, (uint32_t)(aaug >> 32), bauglo, (uint32_t)(baug0 >> 32), IDESC, 1u);
                         umma_commit(BAR(BAR_BEMPTY + ridx));
                         umma_commit(BAR(BAR_ACCFULL + s * 2 + buf));
                     }

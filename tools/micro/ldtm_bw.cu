@@ -24,9 +24,21 @@ __device__ __forceinline__ void ld64(uint32_t taddr, uint32_t (&v)[64]) {
         : "memory");
 }
 
+__device__ __forceinline__ uint64_t desc_sw128(uint32_t saddr) {
+    return (uint64_t)((saddr & 0x3FFFFu) >> 4) | ((uint64_t)1 << 16) | ((uint64_t)(1024 >> 4) << 32) | ((uint64_t)1 << 46) |
+           ((uint64_t)2 << 61);
+}
+
+// mma != 0: warp 15 keeps the tensor pipe busy (M=128, N=128, K=16 fp16 MMAs into TMEM columns 256..383, operands
+// = 32 KB of zeroed shared memory) until the loading warps are done.
 template <int ITER>
-__global__ void __launch_bounds__(512, 1) k(long long *out, uint32_t *sink, int warps) {
+__global__ void __launch_bounds__(512, 1) k(long long *out, uint32_t *sink, int warps, int mma, int mma_n) {
     __shared__ uint32_t slot;
+    __shared__ volatile int done;
+    extern __shared__ __align__(1024) unsigned char opnd[];
+    for (int i = threadIdx.x; i < 32768 / 4; i += blockDim.x) reinterpret_cast<uint32_t *>(opnd)[i] = 0u;
+    if (threadIdx.x == 0) done = 0;
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (warp == 0) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(&slot)), "r"(512u) : "memory");
@@ -51,6 +63,25 @@ __global__ void __launch_bounds__(512, 1) k(long long *out, uint32_t *sink, int 
         }
         t1 = clock64();
     }
+    if (warp < warps && lane == 0) atomicAdd((int *)&done, 1);
+    if (mma && warp == 15) {
+        const uint32_t base = ((uint32_t)__cvta_generic_to_shared(opnd) + 1023u) & ~1023u;
+        const uint64_t ad = desc_sw128(base), bd = desc_sw128(base + 16384);
+        const uint32_t idesc = (1u << 4) | (((uint32_t)mma_n >> 3) << 17) | ((128u >> 4) << 24);
+        long long n = 0;
+        if (lane == 0) {
+            while (done < warps) {
+                for (int i = 0; i < 8; ++i)
+                    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                                 "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem + 256u),
+                                 "l"(ad + (uint64_t)(i & 3) * 2), "l"(bd + (uint64_t)(i & 3) * 2), "r"(idesc), "r"(1u)
+                                 : "memory");
+                n += 8;
+            }
+            out[blockIdx.x * 16 + 15] = n;
+        }
+        __syncwarp();
+    }
     if (lane == 0 && warp < warps) out[blockIdx.x * 16 + warp] = t1 - t0;
     if (acc == 0x12345678u) sink[0] = acc;
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -64,10 +95,13 @@ int main() {
     cudaMalloc(&out, 148 * 16 * 8);
     cudaMalloc(&sink, 4);
     constexpr int ITER = 2048;
-    for (int warps : {1, 4, 8, 16}) {
+    cudaFuncSetAttribute(k<ITER>, cudaFuncAttributeMaxDynamicSharedMemorySize, 66560);
+    for (int mma_n : {64, 128, 256})
+    for (int mma : {1})
+    for (int warps : {4}) {
         for (int rep = 0; rep < 2; ++rep) {
             cudaMemset(out, 0, 148 * 16 * 8);
-            k<ITER><<<148, 512>>>(out, sink, warps);
+            k<ITER><<<148, 512, 66560>>>(out, sink, warps, mma, mma_n);
             cudaError_t e = cudaDeviceSynchronize();
             if (e != cudaSuccess) { printf("error %s\n", cudaGetErrorString(e)); return 1; }
         }
@@ -76,6 +110,7 @@ int main() {
         long long mx = 0;
         for (int w = 0; w < warps; ++w) mx = h[w] > mx ? h[w] : mx;
         const double bytes = (double)warps * ITER * 8192.0;
+        if (mma) printf("meanwhile one lane issued %lld MMAs M=128 N=%d K=16 (%.1f cycles each): ", h[15], mma_n, (double)mx / h[15]);
         printf("%2d warps x %d loads of 32 lanes x 64 columns: %lld cycles -> %.1f B/clk/SM (%.1f cycles per 8 KB load per warp)\n", warps,
                ITER, mx, bytes / mx, (double)mx / ITER);
     }

@@ -696,21 +696,11 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
                     M = max3(M, gb[2], gb[3]);
                     thr = M - twodelta;
                     remember(va, ga, j, 0);
-                    // next accumulator: start its first half now if it is already complete (warp uniform)
-                    const uint32_t nbar = BAR(BAR_ACCFULL + slot * 2 + (buf ^ 1)), npar = ((items + 1) >> 1) & 1u;
-                    bool started = false;
-                    if (j + 1 < NT) {
-                        started = __shfl_sync(0xffffffffu, (int)mbar_probe(nbar, npar), 0) != 0;
-                        if (started) {
-                            tc_fence_after();
-                            tmem_ld64(tq + (buf ^ 1) * 128, va);
-                        }
-                    }
                     remember(vb, gb, j, 1);
-                    RVQ_TL(0x330 | (started ? 1 : 0))
+                    RVQ_TL(0x330)
                     RVQ_LAP(4)
-                    if (j + 1 < NT && !started) {
-                        mbar_wait(nbar, npar);
+                    if (j + 1 < NT) {
+                        mbar_wait(BAR(BAR_ACCFULL + slot * 2 + (buf ^ 1)), ((items + 1) >> 1) & 1u);
                         RVQ_TL(0x340)
                         tc_fence_after();
                         tmem_ld64(tq + (buf ^ 1) * 128, va);

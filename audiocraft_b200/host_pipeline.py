@@ -16,7 +16,7 @@ import torch
 
 
 class HostPipeline:
-    def __init__(self, quantizer, device: tp.Optional[torch.device] = None, chunk_items: int = 16, slots: int = 3):
+    def __init__(self, quantizer, device: tp.Optional[torch.device] = None, chunk_items: int = 32, slots: int = 3):
         self.q = quantizer
         self.device = torch.device(device) if device is not None else next(quantizer.buffers()).device
         if self.device.type != "cuda":

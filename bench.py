@@ -278,7 +278,7 @@ def run_gpu_arm(args, rank: int, world: int, local_rank: int):
     # audiocraft_b200.host_pipeline.HostPipeline: pinned host latents in, pinned host codes + quantized latents
     # out, chunked over copy / compute / copy streams.  Every byte of every step crosses PCIe inside the timed region.
     from audiocraft_b200.host_pipeline import HostPipeline
-    pipe = HostPipeline(m, dev, chunk_items=16)
+    pipe = HostPipeline(m, dev, chunk_items=32)
     x_host = [torch.randn(B, D, T).pin_memory() for _ in range(2)]
     codes_host = [torch.empty((B, K, T), dtype=torch.int64).pin_memory() for _ in range(2)]
     q_host = [torch.empty((B, T, D), dtype=torch.float32).pin_memory() for _ in range(2)]

@@ -10,20 +10,26 @@
 //       pre-swizzled image (rvq_common.cuh) into a 3-deep ring; the residual operand is written to
 //       shared memory by the warps that own the residual.
 //   scan                   each of 128 threads owns one TMEM lane (= one frame) and reduces the 128
-//       columns of an accumulator in groups of 8 codes.  A group is remembered when its maximum is
+//       columns of an accumulator in groups of 16 codes.  A group is remembered when its maximum is
 //       within 2*delta of the running maximum, delta being a rigorous bound on |acc - exact|.
-//   resolve (exact)        every remembered group that is within 2*delta of the final maximum is
-//       re-scored in fp32 in the canonical order (rvq_common.cuh), so the emitted code is the one
-//       the exact scan (rvq_encode_exact.cu) emits, bit for bit.  Frames the bound cannot cover
-//       (non-finite values, extreme scales, list overflow) take a full exact scan in place.
-//   then the residual update r -= E_k[code] in registers, the fp16 operand for the next stage.
+//   resolve (exact)        the codes of the remembered groups whose approximate score is within
+//       2*delta of the final maximum are the only possible winners.  One such code (9 frames in 10):
+//       done.  Two to four: re-scored in fp32 in the canonical order (rvq_common.cuh), eight codes per
+//       batch.  More, or a frame the bound cannot cover (non-finite values, extreme scales, list
+//       overflow): whole groups or the whole codebook re-scored in place.  The emitted code is the
+//       one the exact scan (rvq_encode_exact.cu) emits, bit for bit.
+//   then the residual update r -= E_k[code] through the L2-resident scratch, and the fp16 operand
+//   row of the next stage.
 //
-// A CTA runs two independent 128-frame tiles ("slots") half a stage apart so that the tensor pipe
-// works on one while the other resolves.  Warp roles (12 warps):
-//   warp 0      producer: decides which slot gets the next codebook tile and streams it in
-//   warp 1      tcgen05.mma issuer, owns the TMEM allocation (512 columns: 2 slots x 2 buffers x 128)
+// A CTA runs two 128-frame tiles ("slots") in lock step: both are at the same codebook tile at the
+// same time, so one copy of the tile serves 256 frames.  Warp roles (12 warps):
+//   warp 0      producer: streams the codebook tiles of the CTA, in order, through the ring
+//   warp 1, 2   tcgen05.mma issuers of slot 0 and slot 1 (warp 1 owns the TMEM allocation: 512 columns
+//               = 2 slots x 2 accumulator buffers x 128)
+//   warp 3      idle (setmaxnreg works on whole warpgroups)
 //   warps 4-7   slot 0: residual owners / scanners / resolvers (warp w owns TMEM lanes 32*(w%4)..)
 //   warps 8-11  slot 1
+// profiles/r2_notes.md has the measurements behind this shape and the variants that lost.
 #include <limits.h>
 #include <math_constants.h>
 

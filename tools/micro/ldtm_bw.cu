@@ -64,21 +64,25 @@ __global__ void __launch_bounds__(512, 1) k(long long *out, uint32_t *sink, int 
         t1 = clock64();
     }
     if (warp < warps && lane == 0) atomicAdd((int *)&done, 1);
-    if (mma && warp == 15) {
+    if (mma && (warp == 15 || (mma == 3 && warp == 14))) {
         const uint32_t base = ((uint32_t)__cvta_generic_to_shared(opnd) + 1023u) & ~1023u;
         const uint64_t ad = desc_sw128(base), bd = desc_sw128(base + 16384);
         const uint32_t idesc = (1u << 4) | (((uint32_t)mma_n >> 3) << 17) | ((128u >> 4) << 24);
         long long n = 0;
         if (lane == 0) {
             while (done < warps) {
-                for (int i = 0; i < 8; ++i)
+                for (int i = 0; i < 8; ++i) {
+                    uint32_t dcol = 256u;
+                    if (mma == 2) dcol = (i & 1) ? 384u : 256u;   // one lane, two accumulators in turn
+                    if (mma == 3) dcol = warp == 15 ? 384u : 256u;  // two warps, one accumulator each
                     asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-                                 "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem + 256u),
+                                 "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem + dcol),
                                  "l"(ad + (uint64_t)(i & 3) * 2), "l"(bd + (uint64_t)(i & 3) * 2), "r"(idesc), "r"(1u)
                                  : "memory");
+                }
                 n += 8;
             }
-            out[blockIdx.x * 16 + 15] = n;
+            out[blockIdx.x * 16 + warp] = n;
         }
         __syncwarp();
     }
@@ -96,8 +100,8 @@ int main() {
     cudaMalloc(&sink, 4);
     constexpr int ITER = 2048;
     cudaFuncSetAttribute(k<ITER>, cudaFuncAttributeMaxDynamicSharedMemorySize, 66560);
-    for (int mma_n : {64, 128, 256})
-    for (int mma : {1})
+    for (int mma_n : {128})
+    for (int mma : {1, 2, 3})
     for (int warps : {4}) {
         for (int rep = 0; rep < 2; ++rep) {
             cudaMemset(out, 0, 148 * 16 * 8);
@@ -110,7 +114,7 @@ int main() {
         long long mx = 0;
         for (int w = 0; w < warps; ++w) mx = h[w] > mx ? h[w] : mx;
         const double bytes = (double)warps * ITER * 8192.0;
-        if (mma) printf("meanwhile one lane issued %lld MMAs M=128 N=%d K=16 (%.1f cycles each): ", h[15], mma_n, (double)mx / h[15]);
+        if (mma) printf("mode %d (1: one lane, one accumulator; 2: one lane, two accumulators in turn; 3: two warps, one accumulator each): %lld MMAs M=128 N=%d K=16, %.1f cycles each: ", mma, h[15] + (mma == 3 ? h[14] : 0), mma_n, (double)mx / (h[15] + (mma == 3 ? h[14] : 0)));
         printf("%2d warps x %d loads of 32 lanes x 64 columns: %lld cycles -> %.1f B/clk/SM (%.1f cycles per 8 KB load per warp)\n", warps,
                ITER, mx, bytes / mx, (double)mx / ITER);
     }

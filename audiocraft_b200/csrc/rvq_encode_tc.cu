@@ -800,7 +800,7 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
                 RVQ_TL(0x350)
 #ifdef RVQ_TIMELINE
                 if (P.dbg_acc && n0 + lane < P.N) {  // histogram of candidate counts over all frames (after the event area)
-                    unsigned long long *hist = reinterpret_cast<unsigned long long *>(P.dbg_acc) + 12 * 4096 * 2;
+                    unsigned long long *hist = reinterpret_cast<unsigned long long *>(P.dbg_acc) + 16 * 4096 * 2;
                     atomicAdd(hist + k * 8 + (ncand > 4 ? 5 : ncand), 1ull);
                     atomicAdd(hist + 32 + k * 8 + min(cnt, 17) / 3, 1ull);
                 }

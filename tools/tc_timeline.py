@@ -20,7 +20,7 @@ OUT = os.path.join(ROOT, "tools", "micro", "_build", "librvq_timeline.so")
 def build():
     from audiocraft_b200 import build as b
     os.makedirs(os.path.dirname(OUT), exist_ok=True)
-    cmd = [b._nvcc()] + b.NVCC_FLAGS + ["-DRVQ_TIMELINE", "-shared", "-o", OUT] + b.sources() + ["-lcudart", "-lcuda"]
+    cmd = [b._nvcc()] + b.NVCC_FLAGS + ["-DRVQ_TIMELINE"] + sys.argv[2:] + ["-shared", "-o", OUT] + b.sources() + ["-lcudart", "-lcuda"]
     subprocess.run(cmd, check=True)
     print(OUT)
 
@@ -43,7 +43,7 @@ def run(B=64, T=1500):
     K = 4
     codes = torch.empty((K, B, T), dtype=torch.int64, device="cuda")
     info = torch.zeros((128 * 8 + 192,), device="cuda")
-    tl = torch.zeros((12 * 4096 * 2 + 64,), dtype=torch.int64, device="cuda")
+    tl = torch.zeros((16 * 4096 * 2 + 64,), dtype=torch.int64, device="cuda")
     ws_bytes = lib.rvq_encode_workspace_bytes(B, D, T, K, C, _lib.ALGO_TC)
     ws = torch.empty(ws_bytes, dtype=torch.uint8, device="cuda")
     for _ in range(3):
@@ -54,13 +54,14 @@ def run(B=64, T=1500):
         assert rc == 0, lib.rvq_b200_last_error()
         torch.cuda.synchronize()
     ref = m.encode(x)
-    assert torch.equal(ref, codes.transpose(0, 1)), "timeline build changed the codes"
-    hist = tl[12 * 4096 * 2:].cpu().numpy()
+    if not os.environ.get("RVQ_TL_NOCHECK"):
+        assert torch.equal(ref, codes.transpose(0, 1)), "timeline build changed the codes"
+    hist = tl[16 * 4096 * 2:].cpu().numpy()
     print('candidates per frame (rows: stage; columns: 0,1,2,3,4,more):')
     print(hist[:32].reshape(4, 8)[:, :6])
     print('remembered groups per frame (rows: stage; columns: 0-2,3-5,6-8,9-11,12-14,15+):')
     print(hist[32:].reshape(4, 8)[:, :6])
-    ev = tl[:12 * 4096 * 2].view(12, 4096, 2).cpu().numpy()
+    ev = tl[:16 * 4096 * 2].view(16, 4096, 2).cpu().numpy()
     os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
     np.savez_compressed(os.path.join(ROOT, "gpurun_out", "tc_timeline.npz"), ev=ev)
     digest(ev)

@@ -241,6 +241,20 @@ def run_gpu_arm(args, rank: int, world: int, local_rank: int):
         for i in range(args.warmup):
             step(i)
         sync_all()
+        # W steps are a few milliseconds: keep stepping (untimed) until the GPU has been busy for a quarter of a
+        # second, so that a fresh box (idle clocks, cold L2 / TLBs, first-use work in the driver) is out of the numbers.
+        # The same number of extra steps on every rank: the count is fixed from the measured step time of rank 0.
+        t_w = time.perf_counter()
+        for i in range(20):
+            step(i)
+        sync_all()
+        per_step = max((time.perf_counter() - t_w) / 20, 1e-5)
+        extra = torch.tensor([int(min(2000, max(0, 0.25 / per_step)))], device=dev)
+        if world > 1:
+            dist.broadcast(extra, src=0)
+        for i in range(int(extra.item())):
+            step(i)
+        sync_all()
         ev = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(args.steps)]
         start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         kernels.launch_count(reset=True)
@@ -284,7 +298,7 @@ def run_gpu_arm(args, rank: int, world: int, local_rank: int):
     q_host = [torch.empty((B, T, D), dtype=torch.float32).pin_memory() for _ in range(2)]
 
     with torch.no_grad():
-        for i in range(min(3, args.warmup)):
+        for i in range(max(20, args.warmup)):  # the first host<->device copies of a process are several times slower
             pipe.encode_decode(x_host[i % 2], codes_host[i % 2], q_host[i % 2])
         pipe.synchronize()
         sync_all()
@@ -349,6 +363,11 @@ def run_gpu_arm(args, rank: int, world: int, local_rank: int):
                 "peak": peaks["bf16"], "unit": "TFLOP/s", "frac": round(achieved_tf / peaks["bf16"], 5),
                 "traffic": traffic, "peak_source": peaks["source"] + ", dense bf16 burst",
                 "us_per_launch": round(enc_ms * 1e3, 2)}
+    if peaks.get("bf16_sustained"):
+        # informational: the timed region follows a quarter second of back-to-back steps (the GPU may sit at its
+        # power cap, see "clocks"), the regime of the driver's sustained figure; `frac` stays on the stricter burst peak
+        roofline["peak_sustained"] = peaks["bf16_sustained"]
+        roofline["frac_of_sustained"] = round(achieved_tf / peaks["bf16_sustained"], 5)
     if dec_c4 is not None:
         dec_c4["peak_gbs"] = peaks["hbm"]
         dec_c4["frac"] = round(dec_c4["achieved_gbs"] / peaks["hbm"], 4)
@@ -369,6 +388,7 @@ def run_gpu_arm(args, rank: int, world: int, local_rank: int):
         "config": {"workload": WORKLOAD, "frames_per_gpu_per_step": frames,
                    "l2": f"{N_ROTATING} rotating input batches ({N_ROTATING * h2d // 1000000} MB) > 126 MB L2",
                    "encode_algo": m.vq.encode_algo,
+                   "untimed_steps_before_timing": args.warmup + 20 + int(extra.item()),
                    "collective": "all_gather of the codes per step (int16 on the wire, side stream, all complete inside the timed region)" if world > 1 else "none"},
         "roofline": roofline,
         "cpu_baseline": cpu,

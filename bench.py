@@ -241,15 +241,15 @@ def run_gpu_arm(args, rank: int, world: int, local_rank: int):
         for i in range(args.warmup):
             step(i)
         sync_all()
-        # W steps are a few milliseconds: keep stepping (untimed) until the GPU has been busy for a quarter of a
-        # second, so that a fresh box (idle clocks, cold L2 / TLBs, first-use work in the driver) is out of the numbers.
+        # W steps are a few milliseconds: keep stepping (untimed) until the GPU has been busy for about 60 ms, so
+        # that a fresh box (idle clocks, cold L2 / TLBs, first-use work in the driver) is out of the numbers.
         # The same number of extra steps on every rank: the count is fixed from the measured step time of rank 0.
         t_w = time.perf_counter()
         for i in range(20):
             step(i)
         sync_all()
         per_step = max((time.perf_counter() - t_w) / 20, 1e-5)
-        extra = torch.tensor([int(min(2000, max(0, 0.25 / per_step)))], device=dev)
+        extra = torch.tensor([int(min(2000, max(0, 0.06 / per_step)))], device=dev)
         if world > 1:
             dist.broadcast(extra, src=0)
         for i in range(int(extra.item())):
@@ -364,8 +364,8 @@ def run_gpu_arm(args, rank: int, world: int, local_rank: int):
                 "traffic": traffic, "peak_source": peaks["source"] + ", dense bf16 burst",
                 "us_per_launch": round(enc_ms * 1e3, 2)}
     if peaks.get("bf16_sustained"):
-        # informational: the timed region follows a quarter second of back-to-back steps (the GPU may sit at its
-        # power cap, see "clocks"), the regime of the driver's sustained figure; `frac` stays on the stricter burst peak
+        # informational: under back-to-back steps the GPU may sit at its power cap (see "clocks"), the regime of the
+        # driver's sustained figure; `frac` stays on the stricter burst peak
         roofline["peak_sustained"] = peaks["bf16_sustained"]
         roofline["frac_of_sustained"] = round(achieved_tf / peaks["bf16_sustained"], 5)
     if dec_c4 is not None:

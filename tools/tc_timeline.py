@@ -70,7 +70,7 @@ def run(B=64, T=1500):
 def digest(ev):
     import numpy as np
     t0 = min(int(ev[w, 0, 1]) for w in range(ev.shape[0]) if ev[w, 0, 0])
-    for w in (0, 1, 4, 12):
+    for w in (0, 1, 4, 8):
         n = int((ev[w, :, 0] != 0).sum())
         print(f"warp {w}: {n} events, last at {int(ev[w, n - 1, 1]) - t0}")
     # MMA warp: per item wait for B, wait for accumulator, issue
@@ -94,7 +94,7 @@ def digest(ev):
     w = clk[1::2][: n // 2] - clk[0::2][: n // 2]
     print(f"producer: {n // 2} tiles, wait_b_empty mean {w.mean():.0f} sum {w.sum()}")
     # frame warp 4 (slot 0) and 8 (slot 1): per stage phases
-    for wp in (4, 8, 12):
+    for wp in (4, 8):
         e = ev[wp]
         n = int((e[:, 0] != 0).sum())
         tags, clk = e[:n, 0], e[:n, 1] - t0

@@ -1,8 +1,11 @@
-"""Import the UNMODIFIED reference quantizer from /root/reference (authoring container only).
+"""Import the UNMODIFIED reference quantizer (`audiocraft.quantization`).
 
-TEST INFRASTRUCTURE ONLY.  /root/reference does not exist on the GPU box, so nothing that runs
-there (`-m gpu` tests, smoke(), bench.py) may call this; it is used by tests/golden/make_golden.py
-and by CPU tests that skip when the reference is absent.
+TEST INFRASTRUCTURE ONLY.  Two places can hold it:
+  * /root/reference (authoring container): used by tests/golden/make_golden.py and by CPU tests that skip
+    when the reference is absent;
+  * oracle/_ref/ (git-ignored copy of the four files of the path, staged by oracle/fetch_ref.py and shipped
+    to the GPU box): what `bench.py --impl reference` and bench.py's cpu_baseline leg time on the host cores.
+    /root/reference itself does not exist on the GPU box.
 
 Two obstacles, neither needs a change to the reference:
   * `audiocraft/__init__.py` imports data/models/modules, which need packages that are not
@@ -17,11 +20,32 @@ import os
 import sys
 import types
 
-REFERENCE_ROOT = os.environ.get("RVQ_REFERENCE_ROOT", "/root/reference")
+_STAGED = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref")
+
+
+def _has(root: str) -> bool:
+    return os.path.isfile(os.path.join(root, "audiocraft", "quantization", "core_vq.py"))
+
+
+def _pick_root() -> str:
+    env = os.environ.get("RVQ_REFERENCE_ROOT")
+    if env:
+        return env
+    if _has("/root/reference"):
+        return "/root/reference"
+    if _has(_STAGED):
+        from . import fetch_ref
+        if not fetch_ref.verify():
+            raise RuntimeError("oracle/_ref does not match its manifest: run oracle/fetch_ref.py again")
+        return _STAGED
+    return "/root/reference"
+
+
+REFERENCE_ROOT = _pick_root()
 
 
 def available() -> bool:
-    return os.path.isfile(os.path.join(REFERENCE_ROOT, "audiocraft", "quantization", "core_vq.py"))
+    return _has(REFERENCE_ROOT)
 
 
 def load():

@@ -103,3 +103,19 @@ def test_canonical_dot_definition():
         for off in (16, 8, 4, 2, 1):
             p = (p + p[np.arange(32) ^ off]).astype(np.float32)
         assert np.float32(oracle.dot(a, b)) == p[0]
+
+
+def test_oracle_full_c2_batch_vs_reference():
+    """The whole of BASELINE config 2 (96 000 frames, 384 000 codes) against the unmodified reference's codes:
+    the count of fp32 near-ties is reported and bounded, nothing else may differ."""
+    from tests.golden import make_golden_c2_full as full
+    gold = np.load(os.path.join(os.path.dirname(__file__), "golden", "rvq_golden_c2_full.npz"))
+    x, embed = full.inputs()
+    assert gen.sha(x) == str(gold["x_sha"]) and gen.sha(np.stack(embed)) == str(gold["embed_sha"])
+    want = gold["codes"].astype(np.int64)
+    codes = oracle.encode(x, embed)
+    n_equal, near, wrong, n_cmp = adjudicate(x, embed, codes, want)
+    print(f"oracle vs reference on full c2: {want.size - n_equal} of {want.size} codes differ, {near} near-ties, {wrong} wrong")
+    assert wrong == 0 and near <= 8
+    q = oracle.decode(want, embed)
+    assert gen.sha(np.ascontiguousarray(q.transpose(0, 2, 1))) == str(gold["quant_sha"])

@@ -58,15 +58,10 @@ constexpr int SM_ALLOC = SM_TOTAL + 1024;                  // slack for manual a
 // barrier indices (8 bytes each)
 constexpr int BAR_BFULL = 0;                    // [RING]
 constexpr int BAR_BEMPTY = BAR_BFULL + RING;    // [RING]
-#ifdef RVQ_ATMEM
-constexpr int NACCBAR = 6;                      // [3 buffers][NSLOT]
-#else
-constexpr int NACCBAR = 4;                      // [NSLOT][2]
-#endif
-constexpr int BAR_ACCFULL = BAR_BEMPTY + RING;
-constexpr int BAR_ACCEMPTY = BAR_ACCFULL + NACCBAR;
-constexpr int BAR_AREADY = BAR_ACCEMPTY + NACCBAR;  // [NSLOT]
-constexpr int BAR_COUNT = BAR_AREADY + NSLOT;
+constexpr int BAR_ACCFULL = BAR_BEMPTY + RING;  // [NSLOT][2]
+constexpr int BAR_ACCEMPTY = BAR_ACCFULL + 4;   // [NSLOT][2]
+constexpr int BAR_AREADY = BAR_ACCEMPTY + 4;    // [NSLOT]
+constexpr int BAR_COUNT = BAR_AREADY + NSLOT;   // 16
 constexpr int SM_META = SM_BAR + BAR_COUNT * 8; // ring_meta[RING] (u32), tmem base (u32)
 
 // instruction descriptor: kind::f16, A = B = F16, D = F32, both K-major, M = 128, N = 128
@@ -151,56 +146,6 @@ __device__ __forceinline__ void umma_f16_lh(uint32_t d_tmem, uint32_t alo, uint3
         "r"(alo), "r"(ahi), "r"(blo), "r"(bhi), "r"(idesc), "r"(acc)
         : "memory");
 }
-#ifdef RVQ_ATMEM
-// A operand from tensor memory (lane = frame, 32-bit column = two consecutive fp16 K elements)
-__device__ __forceinline__ void umma_f16_ts(uint32_t d_tmem, uint32_t a_tmem, uint32_t blo, uint32_t bhi, uint32_t idesc,
-                                            uint32_t acc) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t.reg .b64 db;\n\t"
-        "setp.ne.b32 p, %5, 0;\n\t"
-        "mov.b64 db, {%2, %3};\n\t"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], db, %4, p;\n\t}" ::"r"(d_tmem),
-        "r"(a_tmem), "r"(blo), "r"(bhi), "r"(idesc), "r"(acc)
-        : "memory");
-}
-// shared memory -> tensor memory: 128 rows x 32 bytes (one K = 16 slice of a K-major fp16 operand) into 8 columns
-__device__ __forceinline__ void tmem_cp_128x256b(uint32_t taddr, uint32_t dlo, uint32_t dhi) {
-    asm volatile(
-        "{\n\t.reg .b64 da;\n\t"
-        "mov.b64 da, {%1, %2};\n\t"
-        "tcgen05.cp.cta_group::1.128x256b [%0], da;\n\t}" ::"r"(taddr),
-        "r"(dlo), "r"(dhi)
-        : "memory");
-}
-// Three accumulator buffers rotate over the items of a CTA (item = one codebook tile for one slot).  While both
-// slots have tiles the items alternate (slot = index & 1); afterwards every item is slot 0's.  Item i uses
-// buffer i % 3.  Each (buffer, slot) pair has its own "full" and "empty" barrier, so that a waiter is never
-// more than one phase away from the barrier it waits on (with one barrier per buffer a slot that runs ahead
-// of the other would see the parity of a phase two uses back and pass).  Every party walks the same sequence.
-struct ItemWalk {
-    int idx;        // next item
-    int b;          // idx % 3
-    int lim;        // items below this index alternate between the slots
-    uint32_t uses;  // bit b * 2 + t: parity of the number of uses of buffer b by slot t among the items before idx
-    uint32_t hist;  // slots of the last three items (bit 2: item idx - 3)
-    __device__ __forceinline__ void init(int alternating_items) { idx = 0; b = 0; lim = alternating_items; uses = 0; hist = 0; }
-    __device__ __forceinline__ int slot_of_next() const { return idx < lim ? (idx & 1) : 0; }
-    __device__ __forceinline__ void advance() {
-        const int t = slot_of_next();
-        uses ^= 1u << (b * 2 + t);
-        hist = ((hist << 1) | (uint32_t)t) & 7u;
-        b = b == 2 ? 0 : b + 1;
-        ++idx;
-    }
-    __device__ __forceinline__ void seek(int s) { while (slot_of_next() != s) advance(); }  // to slot s's next item
-    // barrier index offsets / parities for the item at idx (slot s)
-    __device__ __forceinline__ int full_bar(int s) const { return b * 2 + s; }
-    __device__ __forceinline__ uint32_t full_par(int s) const { return (uses >> (b * 2 + s)) & 1u; }
-    __device__ __forceinline__ bool has_prev() const { return idx >= 3; }
-    __device__ __forceinline__ int empty_bar() const { return b * 2 + (int)((hist >> 2) & 1u); }  // released by item idx - 3's slot
-    __device__ __forceinline__ uint32_t empty_par() const { return ((uses >> empty_bar()) & 1u) ^ 1u; }
-};
-#endif
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
@@ -222,6 +167,17 @@ __device__ __forceinline__ void tmem_ld64(uint32_t taddr, uint32_t (&v)[64]) {
         : "r"(taddr)
         : "memory");
 }
+// Makes a loop-invariant value opaque to the compiler, so that it stays in a register instead of being
+// recomputed (special-register reads, 64-bit pointer arithmetic) at every use.
+__device__ __forceinline__ uint32_t pin_u32(uint32_t v) {
+    asm volatile("mov.b32 %0, %0;" : "+r"(v));
+    return v;
+}
+template <typename T>
+__device__ __forceinline__ T *pin_ptr(T *p) {
+    asm volatile("mov.b64 %0, %0;" : "+l"(p));
+    return p;
+}
 __device__ __forceinline__ float max3(float a, float b, float c) {
     float r;
     asm("max.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c));
@@ -233,36 +189,21 @@ __device__ __forceinline__ float group_max8(const uint32_t *v) {
     m = max3(m, __uint_as_float(v[5]), __uint_as_float(v[6]));
     return fmaxf(m, __uint_as_float(v[7]));
 }
-// Predicated "remember this group": its 16 approximate scores to the L2 scratch, its packed list word to shared
-// memory.  Straight-line code: a branch per group costs far more than the predicated-off instructions.
+// Predicated "remember this group": its 16 approximate scores to the L2 scratch (two 256-bit stores: every global
+// store of this kernel costs two extra instructions that move its memory descriptor into uniform registers, so
+// fewer and wider stores matter), its packed list word to shared memory.  Straight-line code: a branch per group
+// costs far more than the predicated-off instructions.
 __device__ __forceinline__ void remember_store(bool on, float *gdst, const uint32_t *v, uint32_t sdst, uint32_t word) {
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
         "setp.ne.b32 p, %0, 0;\n\t"
-        "@p st.global.v4.b32 [%1], {%2, %3, %4, %5};\n\t"
-        "@p st.global.v4.b32 [%1+16], {%6, %7, %8, %9};\n\t"
-        "@p st.global.v4.b32 [%1+32], {%10, %11, %12, %13};\n\t"
-        "@p st.global.v4.b32 [%1+48], {%14, %15, %16, %17};\n\t"
+        "@p st.global.v8.b32 [%1], {%2, %3, %4, %5, %6, %7, %8, %9};\n\t"
+        "@p st.global.v8.b32 [%1+32], {%10, %11, %12, %13, %14, %15, %16, %17};\n\t"
         "@p st.shared.b32 [%18], %19;\n\t}"
         ::"r"((int)on), "l"(gdst), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]),
         "r"(v[8]), "r"(v[9]), "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15]), "r"(sdst), "r"(word)
         : "memory");
 }
-#if defined(RVQ_ATMEM) && RVQ_ATMEM == 2
-// registers -> tensor memory: thread t of warp w writes 32 columns of lane 32 * (w % 4) + t
-__device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&v)[32]) {
-    asm volatile(
-        "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
-        "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
-        "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};" ::"r"(taddr),
-        "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]), "r"(v[8]), "r"(v[9]),
-        "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15]), "r"(v[16]), "r"(v[17]), "r"(v[18]),
-        "r"(v[19]), "r"(v[20]), "r"(v[21]), "r"(v[22]), "r"(v[23]), "r"(v[24]), "r"(v[25]), "r"(v[26]), "r"(v[27]),
-        "r"(v[28]), "r"(v[29]), "r"(v[30]), "r"(v[31])
-        : "memory");
-}
-__device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
-#endif
 __device__ __forceinline__ void tmem_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 // K-major SWIZZLE_128B operand: rows of 128 bytes, 8-row groups 1024 bytes apart (SBO), version 1
@@ -487,7 +428,7 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < RING; ++i) { mbar_init(BAR(BAR_BFULL + i), 1); mbar_init(BAR(BAR_BEMPTY + i), NSLOT); }
-        for (int i = 0; i < NACCBAR; ++i) { mbar_init(BAR(BAR_ACCFULL + i), 1); mbar_init(BAR(BAR_ACCEMPTY + i), 4); }
+        for (int i = 0; i < 4; ++i) { mbar_init(BAR(BAR_ACCFULL + i), 1); mbar_init(BAR(BAR_ACCEMPTY + i), 4); }
         for (int i = 0; i < NSLOT; ++i) mbar_init(BAR(BAR_AREADY + i), 4);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -567,67 +508,12 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
             const uint64_t bdesc0 = desc_sw128(base + SM_RING), baug0 = desc_interleaved(base + SM_RING + 32768);
             int j = 0, ridx = 0;
             uint32_t stage_par = 0, rpar = 0;
-#ifdef RVQ_ATMEM
-            ItemWalk iw;
-            iw.init(2 * rounds1 * per_tile);
-            const uint32_t a_tm = tmem + (uint32_t)(384 + s * 64);
-#endif
             for (int n = 0; n < total; ++n) {
                 RVQ_LAP(0)
                 RVQ_TL(0x200)
                 mbar_wait(BAR(BAR_BFULL + ridx), rpar);
                 RVQ_TL(0x210)
                 RVQ_LAP(1)
-#ifdef RVQ_ATMEM
-                if (n < mine) {
-                    if (j == 0) {
-                        // new stage: the slot's operand rows are in shared memory; copy the 128 dims into tensor
-                        // memory (the copies and the MMAs of one thread execute in issue order)
-                        mbar_wait(BAR(BAR_AREADY + s), stage_par);
-                        tc_fence_after();
-#if RVQ_ATMEM == 1
-                        if (elect_one()) {
-#pragma unroll
-                            for (int kb = 0; kb < 2; ++kb)
-#pragma unroll
-                                for (int ks = 0; ks < 4; ++ks)
-                                    tmem_cp_128x256b(a_tm + (uint32_t)((kb * 4 + ks) * 8),
-                                                     (uint32_t)adesc + (uint32_t)(kb * 1024 + ks * 2), (uint32_t)(adesc >> 32));
-                        }
-                        __syncwarp();
-#endif
-                    }
-                    RVQ_LAP(2)
-                    iw.seek(s);
-                    if (iw.has_prev()) mbar_wait(BAR(BAR_ACCEMPTY + iw.empty_bar()), iw.empty_par());
-                    RVQ_LAP(3)
-                    RVQ_TL(0x220 | s)
-                    tc_fence_after();
-                    const uint32_t d = tmem + (uint32_t)(iw.b * 128);
-                    const uint32_t blo = (uint32_t)bdesc0 + (uint32_t)(ridx * (IMG >> 4));
-                    const uint32_t bauglo = (uint32_t)baug0 + (uint32_t)(ridx * (IMG >> 4));
-                    if (elect_one()) {
-#pragma unroll
-                        for (int kb = 0; kb < 2; ++kb)
-#pragma unroll
-                            for (int ks = 0; ks < 4; ++ks)
-                                umma_f16_ts(d, a_tm + (uint32_t)((kb * 4 + ks) * 8), blo + (uint32_t)(kb * 1024 + ks * 2),
-                                            (uint32_t)(bdesc0 >> 32), IDESC, (kb | ks) ? 1u : 0u);
-                        umma_f16_lh(d, (uint32_t)aaug, (uint32_t)(aaug >> 32), bauglo, (uint32_t)(baug0 >> 32), IDESC, 1u);
-                        umma_commit(BAR(BAR_BEMPTY + ridx));
-                        umma_commit(BAR(BAR_ACCFULL + iw.full_bar(s)));
-                    }
-                    __syncwarp();
-                    RVQ_TL(0x230 | s)
-                    iw.advance();
-                    if (++j == NT) { j = 0; stage_par ^= 1u; }
-                } else {
-                    if (elect_one()) mbar_arrive(BAR(BAR_BEMPTY + ridx));
-                    __syncwarp();
-                }
-                if (++ridx == RING) { ridx = 0; rpar ^= 1u; }
-                continue;
-#endif
                 if (n < mine) {
                     if (j == 0) mbar_wait(BAR(BAR_AREADY + s), stage_par);
                     RVQ_LAP(2)
@@ -676,10 +562,6 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
         float4 *rs4 = reinterpret_cast<float4 *>(rs) + lane;  // + f * 32: this lane's 4 dims of frame f
         float *vals = P.vals + (size_t)(cta * NSLOT + slot) * LISTCAP * TILE_M * 16;
         uint32_t items = 0;  // accumulator uses of this slot so far
-#ifdef RVQ_ATMEM
-        ItemWalk iw;
-        iw.init(2 * slot_tiles(P.ntiles, grid, cta, 1) * per_tile);
-#endif
         const bool direct = P.xs_d == 1 && (P.xs_b & 3) == 0 && (P.xs_t & 3) == 0 && ((uintptr_t)P.x & 15) == 0;
 
         for (int tile = cta + grid * slot, first = 1; tile < P.ntiles; tile += 2 * grid, first = 0) {
@@ -767,28 +649,6 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
                     *reinterpret_cast<uint4 *>(ar) = make_uint4(h | (h << 16), h, 0u, 0u);
                     *reinterpret_cast<uint4 *>(ar + 128) = make_uint4(0u, 0u, 0u, 0u);
                 }
-#if defined(RVQ_ATMEM) && RVQ_ATMEM == 2
-                // The 128 dims of this thread's frame go from the shared-memory rows (written lane = 4 dims) into
-                // tensor memory (lane = frame, 64 columns of two fp16 each): the transposition the A-from-TMEM
-                // MMAs need.  The previous stage's MMAs have all completed (their accumulators were consumed).
-                __syncwarp();
-                {
-                    const uint32_t a_dst = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(384 + slot * 64);
-#pragma unroll
-                    for (int kb = 0; kb < 2; ++kb) {
-                        uint32_t v[32];
-                        const uint8_t *rowp = A + kb * 16384 + row_l * 128;
-#pragma unroll
-                        for (int c = 0; c < 8; ++c) {
-                            const uint4 w4 = *reinterpret_cast<const uint4 *>(rowp + ((c ^ (row_l & 7)) << 4));
-                            v[c * 4 + 0] = w4.x; v[c * 4 + 1] = w4.y; v[c * 4 + 2] = w4.z; v[c * 4 + 3] = w4.w;
-                        }
-                        tmem_st32(a_dst + kb * 32, v);
-                    }
-                    tmem_wait_st();
-                    tc_fence_before();
-                }
-#endif
                 fence_proxy_async();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(BAR(BAR_AREADY + slot));
@@ -801,19 +661,21 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
                 int cnt = 0;
                 const bool dbg = DBG && cta == 0 && slot == 0 && first && k == P.dbg_stage;
                 RVQ_LAP(2)
-                // One accumulator = 128 codes = two TMEM loads of 64 columns.  While one half is reduced the
-                // next half (of this accumulator, or of the next one if it is already complete) is in flight;
-                // the accumulator is handed back to the MMA warp as soon as both halves are in registers.
+                // One accumulator = 128 codes = two TMEM loads of 64 columns, and one load is always in flight
+                // while the other half is reduced: the second half of this accumulator during the first, the first
+                // half of the next accumulator during the second.  The accumulator is handed back to the MMA warp
+                // as soon as both halves are in registers.  (A half is judged against the maximum seen up to and
+                // including itself: a lower threshold than the final one only remembers more groups.)
                 // group maxima of one 64-column half (independent dependency chains)
                 auto half_max = [&](const uint32_t(&v)[64], float(&gmx)[4]) {
 #pragma unroll
                     for (int g = 0; g < 4; ++g) gmx[g] = fmaxf(group_max8(&v[16 * g]), group_max8(&v[16 * g + 8]));
                 };
                 // remember the groups of one half that are within 2*delta of the maximum seen so far
-                // (which already includes this whole accumulator)
-                float *vals_row = vals + (size_t)row_l * 16;             // + cnt * TILE_M * 16
-                const uint32_t list_row = smem_u32(list + row_l);        // + cnt * TILE_M * 4
+                float *vals_row = pin_ptr(vals + (size_t)row_l * 16);       // + cnt * TILE_M * 16
+                const uint32_t list_row = pin_u32(smem_u32(list + row_l));  // + cnt * TILE_M * 4
                 auto remember = [&](const uint32_t(&v)[64], const float(&gmx)[4], int j, int half) {
+                    const uint32_t idb = (uint32_t)(j * 8 + half * 4);
 #pragma unroll
                     for (int g = 0; g < 4; ++g) {
                         const uint32_t *vg = &v[16 * g];
@@ -825,76 +687,45 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
                         const bool pass = gmx[g] >= thr;
                         remember_store(pass && cnt < LISTCAP, vals_row + (size_t)cnt * (TILE_M * 16), vg,
                                        list_row + (uint32_t)cnt * (TILE_M * 4),
-                                       (__float_as_uint(gmx[g]) & ~0x7FFu) | (uint32_t)(j * 8 + half * 4 + g));
+                                       (__float_as_uint(gmx[g]) & ~0x7FFu) | (idb + (uint32_t)g));
                         cnt += pass ? 1 : 0;
                     }
                 };
-#ifdef RVQ_ATMEM
-                const uint32_t tq = tmem + ((uint32_t)(q * 32) << 16);
                 uint32_t va[64], vb[64];
-                iw.seek(slot);
-                mbar_wait(BAR(BAR_ACCFULL + iw.full_bar(slot)), iw.full_par(slot));
-                tc_fence_after();
-                tmem_ld64(tq + iw.b * 128, va);
-                for (int j = 0; j < NT; ++j, ++items) {
-                    const int buf = iw.b;
-                    float ga[4], gb[4];
-                    RVQ_TL(0x310)
-                    tmem_wait_ld();
-                    tmem_ld64(tq + buf * 128 + 64, vb);
-                    RVQ_TL(0x320)
-                    RVQ_LAP(3)
-                    half_max(va, ga);
-                    tmem_wait_ld();
-                    tc_fence_before();
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive(BAR(BAR_ACCEMPTY + buf * 2 + slot));
-                    iw.advance();
-#else
-                const uint32_t tq = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(slot * 256);
-                uint32_t va[64], vb[64];
-                mbar_wait(BAR(BAR_ACCFULL + slot * 2 + (items & 1)), (items >> 1) & 1u);
+                const uint32_t tq = pin_u32(tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(slot * 256));
+                const uint32_t bar_full = pin_u32(BAR(BAR_ACCFULL + slot * 2)), bar_empty = pin_u32(BAR(BAR_ACCEMPTY + slot * 2));
+                mbar_wait(bar_full + 8u * (items & 1u), (items >> 1) & 1u);
                 tc_fence_after();
                 tmem_ld64(tq + (items & 1) * 128, va);
                 for (int j = 0; j < NT; ++j, ++items) {
-                    const int buf = items & 1;
                     float ga[4], gb[4];
+                    const int buf = items & 1;
                     RVQ_TL(0x310)
                     tmem_wait_ld();
                     tmem_ld64(tq + buf * 128 + 64, vb);
                     RVQ_TL(0x320)
                     RVQ_LAP(3)
                     half_max(va, ga);
+                    M = fmaxf(M, fmaxf(fmaxf(ga[0], ga[1]), fmaxf(ga[2], ga[3])));
+                    thr = M - twodelta;
+                    remember(va, ga, j, 0);
                     tmem_wait_ld();
                     tc_fence_before();
                     __syncwarp();
-                    if (lane == 0) mbar_arrive(BAR(BAR_ACCEMPTY + slot * 2 + buf));
-#endif
-                    half_max(vb, gb);
-                    // the threshold uses the maximum over everything up to and including this accumulator
-                    M = fmaxf(M, fmaxf(max3(ga[0], ga[1], ga[2]), max3(ga[3], gb[0], gb[1])));
-                    M = max3(M, gb[2], gb[3]);
-                    thr = M - twodelta;
-                    remember(va, ga, j, 0);
-                    remember(vb, gb, j, 1);
-                    RVQ_TL(0x330)
+                    if (lane == 0) mbar_arrive(bar_empty + 8u * (uint32_t)buf);
                     RVQ_LAP(4)
-#ifdef RVQ_ATMEM
                     if (j + 1 < NT) {
-                        iw.seek(slot);
-                        mbar_wait(BAR(BAR_ACCFULL + iw.full_bar(slot)), iw.full_par(slot));
-                        RVQ_TL(0x340)
-                        tc_fence_after();
-                        tmem_ld64(tq + iw.b * 128, va);
-                    }
-#else
-                    if (j + 1 < NT) {
-                        mbar_wait(BAR(BAR_ACCFULL + slot * 2 + (buf ^ 1)), ((items + 1) >> 1) & 1u);
+                        // the first half of the next accumulator travels while the second half of this one is reduced
+                        mbar_wait(bar_full + 8u * (uint32_t)(buf ^ 1), ((items + 1) >> 1) & 1u);
                         RVQ_TL(0x340)
                         tc_fence_after();
                         tmem_ld64(tq + (buf ^ 1) * 128, va);
                     }
-#endif
+                    half_max(vb, gb);
+                    M = fmaxf(M, fmaxf(fmaxf(gb[0], gb[1]), fmaxf(gb[2], gb[3])));
+                    thr = M - twodelta;
+                    remember(vb, gb, j, 1);
+                    RVQ_TL(0x330)
                 }
                 if (DBG && dbg) {
                     float *o = P.dbg_info + row_l * 8;

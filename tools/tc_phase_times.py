@@ -6,6 +6,8 @@ from audiocraft_b200 import _lib
 from audiocraft_b200.quantization import ResidualVectorQuantizer
 
 B, T = int(sys.argv[1]) if len(sys.argv) > 1 else 64, 1500
+if len(sys.argv) > 2:  # a variant library built by tools/variant.py
+    _lib.LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "micro", "_build", f"librvq_{sys.argv[2]}.so")
 torch.manual_seed(0)
 m = ResidualVectorQuantizer(dimension=128, n_q=4, bins=2048, kmeans_init=False).cuda().eval()
 x = torch.randn(B, 128, T, device="cuda")

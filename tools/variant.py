@@ -117,6 +117,26 @@ def one(name):
         calls[i % 4]()
     b.record()
     torch.cuda.synchronize()
+    if os.environ.get("RVQ_ROUNDS"):
+        # kernel time by round structure: 148 single-slot tiles, one and two full pair rounds, config 2's 750 tiles
+        for label, B, T in [("148 tiles (one slot per CTA)", 148, 128), ("296 tiles (one pair round)", 296, 128),
+                            ("444 tiles (pair + single)", 444, 128), ("592 tiles (two pair rounds)", 592, 128)]:
+            x = torch.randn(B, 128, T, device="cuda")
+            call, _ = encode_with(lib, m, x, 4, _lib.ALGO_TC)
+            for _ in range(3):
+                call()
+            torch.cuda.synchronize()
+            tt = []
+            for _ in range(15):
+                e0 = torch.cuda.Event(enable_timing=True)
+                e1 = torch.cuda.Event(enable_timing=True)
+                e0.record()
+                call()
+                e1.record()
+                torch.cuda.synchronize()
+                tt.append(e0.elapsed_time(e1))
+            tt.sort()
+            print(f"[{name}]   {label}: med {tt[len(tt) // 2]:.4f} ms", flush=True)
     print(f"[{name}] parity {'ok' if ok else 'FAILED'}  c2 encode: min {ts[0]:.4f} med {ts[len(ts) // 2]:.4f} "
           f"max {ts[-1]:.4f} ms; back to back {a.elapsed_time(b) / 40:.4f} ms", flush=True)
     return 0 if ok else 2

@@ -18,10 +18,11 @@ RVQ_ECUDA = -3
 RVQ_EPACK = -4
 
 ALGO_AUTO, ALGO_EXACT, ALGO_TC = 0, 1, 2
-ABI_VERSION = 1
+ABI_VERSION = 2
 
 _i32, _i64, _vp = ctypes.c_int, ctypes.c_int64, ctypes.c_void_p
 _i64x3 = ctypes.c_int64 * 3
+_i64x2 = ctypes.c_int64 * 2
 
 # name -> (restype, argtypes); must list every symbol include/rvq_b200.h declares
 SIGNATURES = {
@@ -33,6 +34,18 @@ SIGNATURES = {
     "rvq_encode_workspace_bytes": (_i64, [_i32, _i32, _i32, _i32, _i32, _i32]),
     "rvq_encode_f32": (_i32, [_vp, _i64x3, _i32, _i32, _i32, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _i64,
                               _i32, _vp]),
+    "rvq_encode_f32_wire": (_i32, [_vp, _i64x3, _i32, _i32, _i32, _vp, _i32, _i32, _i32, _vp, _vp, _i64x2, _vp, _vp, _i64,
+                                   _i32, _vp]),
+    "rvq_widen_codes_i16": (_i32, [_vp, _i32, _i32, _i32, _i32, _i32, _vp, _vp]),
+    "rvq_codes_convert": (_i32, [_vp, _i32, _i64x3, _i32, _i32, _i32, _vp, _i32, _i64x3, _vp]),
+    "rvq_codes_packed_bytes": (_i64, [_i64, _i32]),
+    "rvq_codes_pack_bits": (_i32, [_vp, _i64, _i32, _vp, _vp]),
+    "rvq_codes_unpack_bits": (_i32, [_vp, _i64, _i32, _vp, _vp]),
+    "rvq_stereo_interleave": (_i32, [_vp, _vp, _i64x3, _i32, _i32, _i32, _i32, _vp, _vp]),
+    "rvq_stereo_split": (_i32, [_vp, _i32, _i32, _i32, _i32, _vp, _vp, _vp]),
+    "rvq_delay_build": (_i32, [_vp, _i64x3, _i32, _i32, _i32, _i32, ctypes.POINTER(_i32), _i32, _i64, _vp, _vp, _vp, _vp]),
+    "rvq_delay_revert": (_i32, [_vp, _i64x3, _i32, _i32, _i32, _i32, _i32, ctypes.POINTER(_i32), _i32, _i64, _vp, _vp,
+                                _vp, _vp]),
     "rvq_encode_f32_static": (_i32, [_vp, _i64x3, _i32, _i32, _i32, _vp, _i32, _i32, _i32, _vp, _vp, _vp]),
     "rvq_debug_tc_scores": (_i32, [_vp, _i64x3, _i32, _i32, _i32, _vp, _i32, _i32, _i32, _i32, _vp, _vp, _vp, _vp,
                                    _i64, _vp]),

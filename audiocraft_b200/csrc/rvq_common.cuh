@@ -85,6 +85,13 @@ static inline __host__ RvqPackView rvq_pack_view(const void *pack, int Ktot, int
     return v;
 }
 
+// Optional second output of the encode kernels: the codes as int16 in the layout a frame-sharded job puts on the
+// wire (element (k, b, t) at p[k * sk + b * sb + t]; p == nullptr: not wanted).
+struct RvqWire {
+    int16_t *p;
+    int64_t sk, sb;
+};
+
 // ---- error plumbing (host) ----
 void rvq_set_error(const char *fmt, ...);
 void rvq_count_launch(int n);

@@ -142,8 +142,8 @@ static int launch_decode_k(const void *codes, const int64_t cs[3], int B, int K,
                            float *out, const int64_t os[3], int64_t *status, cudaStream_t stream) {
     const int64_t ngroups = (int64_t)B * ((T + 31) / 32);
     int dev = 0, sms = 148;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    RVQ_CUDA(cudaGetDevice(&dev));
+    RVQ_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     const int KP = (K + 3) & ~3;
     const int wpb = KP <= 32 ? 8 : 4;
     const size_t smem = (size_t)wpb * KP * 32 * sizeof(int);

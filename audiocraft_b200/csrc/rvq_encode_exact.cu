@@ -37,7 +37,7 @@ template <int DCH, int F>
 __global__ void __launch_bounds__(RVQ_EX_WARPS * 32)
 rvq_encode_exact_kernel(const float *__restrict__ x, int64_t xs_b, int64_t xs_d, int64_t xs_t, int B, int D, int T,
                         const float *__restrict__ embed, const float *__restrict__ cnorm, int C, int K,
-                        int64_t *__restrict__ codes, float *__restrict__ quantized) {
+                        int64_t *__restrict__ codes, float *__restrict__ quantized, const RvqWire wire) {
     extern __shared__ float4 s_tile[];  // [RVQ_EX_ROWS][DCH * 32] float4
     const int lane = threadIdx.x & 31;
     const int wib = threadIdx.x >> 5;
@@ -130,7 +130,10 @@ rvq_encode_exact_kernel(const float *__restrict__ x, int64_t xs_b, int64_t xs_d,
             }
             const int64_t n = n0 + f;
             if (n < N) {
-                if (lane == 0) codes[(int64_t)k * N + n] = (int64_t)bi;  // [K][B][T]
+                if (lane == 0) {
+                    codes[(int64_t)k * N + n] = (int64_t)bi;  // [K][B][T]
+                    if (wire.p) wire.p[(int64_t)k * wire.sk + (n / T) * wire.sb + (n % T)] = (int16_t)bi;
+                }
 #pragma unroll
                 for (int ch = 0; ch < DCH; ++ch) {
                     const int d = ch * 128 + lane * 4;
@@ -165,7 +168,7 @@ rvq_encode_exact_kernel(const float *__restrict__ x, int64_t xs_b, int64_t xs_d,
 
 template <int DCH, int F>
 static int launch_exact(const float *x, const int64_t xs[3], int B, int D, int T, const RvqPackView &pv, int K,
-                        int64_t *codes, float *quantized, cudaStream_t stream) {
+                        int64_t *codes, float *quantized, const RvqWire &wire, cudaStream_t stream) {
     const int64_t N = (int64_t)B * T;
     const int64_t per_block = (int64_t)RVQ_EX_WARPS * F;
     const int64_t blocks = (N + per_block - 1) / per_block;
@@ -173,17 +176,17 @@ static int launch_exact(const float *x, const int64_t xs[3], int B, int D, int T
     auto kern = rvq_encode_exact_kernel<DCH, F>;
     if (smem > 48 * 1024) RVQ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     kern<<<(unsigned)blocks, RVQ_EX_WARPS * 32, smem, stream>>>(x, xs[0], xs[1], xs[2], B, D, T, pv.embed, pv.cnorm,
-                                                                pv.C, K, codes, quantized);
+                                                                pv.C, K, codes, quantized, wire);
     rvq_count_launch(1);
     return rvq_check_launch("rvq_encode_exact_kernel");
 }
 
 int rvq_encode_exact(const float *x, const int64_t xs[3], int B, int D, int T, const RvqPackView &pv, int K,
-                     int64_t *codes, float *quantized, cudaStream_t stream) {
+                     int64_t *codes, float *quantized, const RvqWire &wire, cudaStream_t stream) {
     RVQ_REQUIRE(D <= 512, RVQ_EUNSUPPORTED, "rvq_encode_f32: dimension %d > 512 is not implemented", D);
     RVQ_REQUIRE((int64_t)B * T <= (int64_t)INT_MAX * 8, RVQ_EUNSUPPORTED, "rvq_encode_f32: too many frames");
-    if (D <= 128) return launch_exact<1, 2>(x, xs, B, D, T, pv, K, codes, quantized, stream);
-    if (D <= 256) return launch_exact<2, 1>(x, xs, B, D, T, pv, K, codes, quantized, stream);
-    if (D <= 384) return launch_exact<3, 1>(x, xs, B, D, T, pv, K, codes, quantized, stream);
-    return launch_exact<4, 1>(x, xs, B, D, T, pv, K, codes, quantized, stream);
+    if (D <= 128) return launch_exact<1, 2>(x, xs, B, D, T, pv, K, codes, quantized, wire, stream);
+    if (D <= 256) return launch_exact<2, 1>(x, xs, B, D, T, pv, K, codes, quantized, wire, stream);
+    if (D <= 384) return launch_exact<3, 1>(x, xs, B, D, T, pv, K, codes, quantized, wire, stream);
+    return launch_exact<4, 1>(x, xs, B, D, T, pv, K, codes, quantized, wire, stream);
 }

@@ -399,6 +399,7 @@ struct TcParams {
     const RvqStageMeta *meta;
     int C, K, NT;         // NT = C / 128
     int64_t *codes;       // [K][N]
+    RvqWire wire;         // optional int16 copy of the codes (frame-sharded jobs)
     float *scratch;       // residuals of the tiles in flight: [grid][2 slots][128 frames][128] fp32
     float *vals;          // approximate scores of the remembered groups: [grid][2 slots][LISTCAP][128 frames][16]
     // diagnostics (optional): accumulators and per-frame scan state of CTA 0 / slot 0 / first tile
@@ -570,6 +571,7 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
             // lane = frame: where this lane's frame starts in x (-1: past the end)
             const int64_t n_l = n0 + lane;
             const int64_t xoff = n_l < P.N ? (n_l / P.T) * P.xs_b + (n_l % P.T) * P.xs_t : -1;
+            const int64_t woff = (P.wire.p && n_l < P.N) ? (n_l / P.T) * P.wire.sb + (n_l % P.T) : -1;
             if (!direct) {
                 // lane = frame reads (coalesced when T is the contiguous axis), transposed 32 dims at a
                 // time through this warp's own 4 KB of the A tile into the scratch rows
@@ -985,6 +987,7 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
                     }
                 }
                 if (n0 + lane < P.N) P.codes[(int64_t)k * P.N + n0 + lane] = (int64_t)mycode;
+                if (woff >= 0) P.wire.p[(int64_t)k * P.wire.sk + woff] = (int16_t)mycode;
                 xx = xx_next;
                 __syncwarp();
                 RVQ_TL(0x370)
@@ -1042,7 +1045,7 @@ int rvq_decode_launch_internal(const int64_t *codes_kbt, int B, int K, int T, co
                                int64_t *status, cudaStream_t stream);
 
 static int launch_tc(const float *x, const int64_t xs[3], int B, int T, const RvqPackView &pv, int K, int64_t *codes,
-                     void *workspace, int64_t workspace_bytes, float *dbg_acc, float *dbg_info, int dbg_stage,
+                     const RvqWire &wire, void *workspace, int64_t workspace_bytes, float *dbg_acc, float *dbg_info, int dbg_stage,
                      cudaStream_t stream, bool fit_grid_to_workspace = false) {
     TcParams P;
     P.x = x; P.xs_b = xs[0]; P.xs_d = xs[1]; P.xs_t = xs[2];
@@ -1052,6 +1055,7 @@ static int launch_tc(const float *x, const int64_t xs[3], int B, int T, const Rv
     P.img = pv.img; P.embed = pv.embed; P.cnorm = pv.cnorm; P.meta = pv.meta;
     P.C = pv.C; P.K = K; P.NT = pv.C / 128;
     P.codes = codes;
+    P.wire = wire;
     P.dbg_acc = dbg_acc; P.dbg_info = dbg_info; P.dbg_stage = dbg_stage;
     P.dbg_time = dbg_info ? reinterpret_cast<long long *>(dbg_info + 128 * 8) : nullptr;  // info_out: 128*8 floats + 96 int64
     int sms = 0;
@@ -1085,10 +1089,10 @@ static int launch_tc(const float *x, const int64_t xs[3], int B, int T, const Rv
 }
 
 int rvq_encode_tc(const float *x, const int64_t xs[3], int B, int D, int T, const void *pack, const RvqPackView &pv,
-                  int K, int64_t *codes, float *quantized, void *workspace, int64_t workspace_bytes,
+                  int K, int64_t *codes, float *quantized, const RvqWire &wire, void *workspace, int64_t workspace_bytes,
                   cudaStream_t stream, bool fit_grid_to_workspace) {
     (void)pack; (void)D;
-    int rc = launch_tc(x, xs, B, T, pv, K, codes, workspace, workspace_bytes, nullptr, nullptr, 0, stream,
+    int rc = launch_tc(x, xs, B, T, pv, K, codes, wire, workspace, workspace_bytes, nullptr, nullptr, 0, stream,
                        fit_grid_to_workspace);
     if (rc != RVQ_OK || !quantized) return rc;
     // quantized_out = 0 + q_0 + ... (core_vq.py:363-385): the gather-sum kernel on the codes just written
@@ -1104,7 +1108,7 @@ extern "C" int rvq_debug_tc_scores(const float *x, const int64_t xs[3], int B, i
     RVQ_REQUIRE(rvq_tc_shape_supported(D, C) && K > 0 && K <= Ktot && stage >= 0 && stage < K, RVQ_EUNSUPPORTED,
                 "rvq_debug_tc_scores: shape not covered by the tensor-core path");
     RvqPackView pv = rvq_pack_view(pack, Ktot, C, D);
-    return launch_tc(x, xs, B, T, pv, K, codes, workspace, workspace_bytes, acc_out, info_out, stage,
+    return launch_tc(x, xs, B, T, pv, K, codes, RvqWire{nullptr, 0, 0}, workspace, workspace_bytes, acc_out, info_out, stage,
                      (cudaStream_t)stream_);
 }
 
@@ -1112,6 +1116,7 @@ extern "C" int rvq_debug_tc_scores(const float *x, const int64_t xs[3], int B, i
 // Scratch for rvq_encode_f32_static: the same layout rvq_encode_f32 expects in its caller-provided workspace,
 // sized for RVQ_STATIC_MAX_FRAMES frames (16 CTAs of two 128-frame tiles).  It lives in the module image, so
 // every GPU that loads the library carries these ~6 MB until the process exits.
+static_assert(RVQ_STATIC_MAX_FRAMES % (NSLOT * TILE_M) == 0, "the frame limit must be a whole number of CTA rounds");
 static constexpr int STATIC_CTAS = RVQ_STATIC_MAX_FRAMES / (NSLOT * TILE_M);
 static __device__ __align__(256) unsigned char g_static_scratch[WS_HEADER + WS_PER_CTA * STATIC_CTAS];
 
@@ -1157,6 +1162,7 @@ extern "C" int rvq_encode_f32_static(const float *x, const int64_t xs[3], int B,
     RvqPackView pv = rvq_pack_view(pack, Ktot, C, D);
     // The array still holds what the previous call left.  The residual / score areas are fully rewritten before
     // they are read; the status word of the gather-sum kernel must start at zero and is cleared inside rvq_encode_tc.
-    return rvq_encode_tc(x, xs, B, D, T, pack, pv, K, codes, quantized, scratch, (int64_t)sizeof(g_static_scratch), stream,
+    return rvq_encode_tc(x, xs, B, D, T, pack, pv, K, codes, quantized, RvqWire{nullptr, 0, 0}, scratch,
+                         (int64_t)sizeof(g_static_scratch), stream,
                          /*fit_grid_to_workspace=*/true);
 }

@@ -31,11 +31,19 @@ class HostPipeline:
         self._next_slot = 0
 
     def _staging(self, D: int, T: int) -> None:
-        shape = (self.chunk_items, D, T)
-        if not self._x_dev or tuple(self._x_dev[0].shape) != shape:
-            self._x_dev = [torch.empty(shape, dtype=torch.float32, device=self.device) for _ in range(self.slots)]
-            self._free = [None] * self.slots
-            self._next_slot = 0
+        """Staging slots hold `chunk_items * D * T` floats and only ever grow: a call with shorter items uses views of
+        the same memory.  When they do have to grow, the copies and kernels that still use the old slots are waited
+        for first (the old blocks go back to the allocator, which may hand them out again at once)."""
+        need = self.chunk_items * D * T
+        if self._x_dev and self._x_dev[0].numel() >= need:
+            return
+        for ev in self._free:
+            if ev is not None:
+                ev.synchronize()
+        self.s_in.synchronize()
+        self._x_dev = [torch.empty(need, dtype=torch.float32, device=self.device) for _ in range(self.slots)]
+        self._free = [None] * self.slots
+        self._next_slot = 0
 
     @torch.no_grad()
     def encode_decode(self, x_host: torch.Tensor, codes_host: torch.Tensor, quant_host: torch.Tensor) -> torch.cuda.Event:
@@ -56,11 +64,20 @@ class HostPipeline:
         cur = torch.cuda.current_stream(self.device)
         self.s_in.wait_stream(cur)  # whatever produced the host data on the caller's stream is done first
         last = None
+        try:
+            last = self._run_chunks(x_host, codes_host, quant_host, B, D, T)
+        finally:
+            if saved is not None:
+                vq.check_codes = saved
+        return last
+
+    def _run_chunks(self, x_host, codes_host, quant_host, B, D, T):
+        last = None
         for lo in range(0, B, self.chunk_items):
             hi = min(B, lo + self.chunk_items)
             slot = self._next_slot
             self._next_slot = (slot + 1) % self.slots
-            xd = self._x_dev[slot][: hi - lo]
+            xd = self._x_dev[slot][: (hi - lo) * D * T].view(hi - lo, D, T)
             with torch.cuda.stream(self.s_in):
                 if self._free[slot] is not None:
                     self.s_in.wait_event(self._free[slot])  # the kernels that read this staging slot last
@@ -84,8 +101,6 @@ class HostPipeline:
                 quant.record_stream(self.s_out)
                 last = torch.cuda.Event(enable_timing=True)
                 last.record(self.s_out)
-        if saved is not None:
-            vq.check_codes = saved
         return last
 
     def synchronize(self) -> None:

@@ -55,9 +55,11 @@ def pack_codebooks(embeds: tp.Sequence[torch.Tensor]) -> torch.Tensor:
 
 
 def encode(x: torch.Tensor, pack: torch.Tensor, Ktot: int, C: int, K: int, want_quantized: bool = False,
-           algo: str = "auto") -> tp.Tuple[torch.Tensor, tp.Optional[torch.Tensor]]:
+           algo: str = "auto", wire: tp.Optional[torch.Tensor] = None
+           ) -> tp.Tuple[torch.Tensor, tp.Optional[torch.Tensor]]:
     """x [B, D, T] fp32 (any strides) -> codes [K, B, T] int64 and, optionally, the summed
-    quantized latent as a contiguous [B, T, D] tensor."""
+    quantized latent as a contiguous [B, T, D] tensor.  `wire`: an int16 [K, B, T] view (time axis contiguous, any
+    k / b strides) that receives the same codes in the wire format of a frame-sharded job."""
     lib = _lib.load()
     _require_cuda(x, "x")
     if x.dtype != torch.float32:
@@ -75,9 +77,19 @@ def encode(x: torch.Tensor, pack: torch.Tensor, Ktot: int, C: int, K: int, want_
             ws_bytes = lib.rvq_encode_workspace_bytes(B, D, T, K, C, a)
             _lib.check(ws_bytes, "rvq_encode_workspace_bytes")
             ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev) if ws_bytes > 0 else None
-            rc = lib.rvq_encode_f32(x.data_ptr(), _lib.strides3(x.stride()), B, D, T, pack.data_ptr(), Ktot, C, K,
-                                    codes.data_ptr(), quant.data_ptr() if quant is not None else None,
-                                    ws.data_ptr() if ws is not None else None, ws_bytes, a, _stream(dev))
+            qp = quant.data_ptr() if quant is not None else None
+            wp = ws.data_ptr() if ws is not None else None
+            if wire is None:
+                rc = lib.rvq_encode_f32(x.data_ptr(), _lib.strides3(x.stride()), B, D, T, pack.data_ptr(), Ktot, C, K,
+                                        codes.data_ptr(), qp, wp, ws_bytes, a, _stream(dev))
+            else:
+                if wire.dtype != torch.int16 or tuple(wire.shape) != (K, B, T) or wire.device != dev or \
+                        (T > 1 and wire.stride(2) != 1):
+                    raise ValueError("wire must be an int16 [K, B, T] view on x's device with a contiguous time axis")
+                rc = lib.rvq_encode_f32_wire(x.data_ptr(), _lib.strides3(x.stride()), B, D, T, pack.data_ptr(), Ktot, C,
+                                             K, codes.data_ptr(), wire.data_ptr(),
+                                             _lib._i64x2(int(wire.stride(0)), int(wire.stride(1))), qp, wp, ws_bytes, a,
+                                             _stream(dev))
             _lib.check(rc, "rvq_encode_f32")
         elif quant is not None:
             quant.zero_()
@@ -107,3 +119,137 @@ def decode(codes: torch.Tensor, pack: torch.Tensor, Ktot: int, C: int, D: int, s
                                     status.data_ptr(), _stream(dev))
             _lib.check(rc, "rvq_decode_f32")
     return out
+
+
+# ---- code-stream plumbing (include/rvq_b200.h, csrc/rvq_codestream.cu) ------------------------------------------
+def _require_codes(t: torch.Tensor, what: str, dtype=torch.int64) -> None:
+    _require_cuda(t, what)
+    if t.dtype != dtype:
+        raise RuntimeError(f"{what} must be {dtype}, got {t.dtype}")
+
+
+def widen_codes_i16(recv: torch.Tensor, W: int, K: int, B: int, T: int, axis: int) -> torch.Tensor:
+    """All-gathered int16 codes (W ranks x padded shard, see rvq_widen_codes_i16) -> int64 [K, B, T]."""
+    lib = _lib.load()
+    _require_codes(recv, "recv", torch.int16)
+    dev = recv.device
+    with torch.cuda.device(dev):
+        out = torch.empty((K, B, T), dtype=torch.int64, device=dev)
+        rc = lib.rvq_widen_codes_i16(recv.data_ptr(), W, K, B, T, axis, out.data_ptr(), _stream(dev))
+    _lib.check(rc, "rvq_widen_codes_i16")
+    return out
+
+
+_CODE_BYTES = {torch.int64: 8, torch.int32: 4, torch.int16: 2}
+
+
+def convert_codes(codes: torch.Tensor, dtype: torch.dtype, out: tp.Optional[torch.Tensor] = None) -> torch.Tensor:
+    """[B, K, T] codes (any strides; int64 / int32 / int16) -> contiguous [B, K, T] of `dtype`, or into `out`
+    (same shape, any strides)."""
+    lib = _lib.load()
+    _require_cuda(codes, "codes")
+    if codes.dtype not in _CODE_BYTES or dtype not in _CODE_BYTES or codes.dim() != 3:
+        raise ValueError("codes must be a 3-d int64 / int32 / int16 tensor")
+    B, K, T = codes.shape
+    dev = codes.device
+    with torch.cuda.device(dev):
+        if out is None:
+            out = torch.empty((B, K, T), dtype=dtype, device=dev)
+        rc = lib.rvq_codes_convert(codes.data_ptr(), _CODE_BYTES[codes.dtype], _lib.strides3(codes.stride()), B, K, T,
+                                   out.data_ptr(), _CODE_BYTES[out.dtype], _lib.strides3(out.stride()), _stream(dev))
+    _lib.check(rc, "rvq_codes_convert")
+    return out
+
+
+def pack_codes(codes: torch.Tensor, bits: int) -> torch.Tensor:
+    """Contiguous int64 codes (any shape) -> uint8 [ceil(n * bits / 8)]."""
+    lib = _lib.load()
+    _require_codes(codes, "codes")
+    c = codes if codes.is_contiguous() else codes.contiguous()
+    n = c.numel()
+    nbytes = lib.rvq_codes_packed_bytes(n, bits)
+    _lib.check(nbytes, "rvq_codes_packed_bytes")
+    with torch.cuda.device(c.device):
+        out = torch.empty(nbytes, dtype=torch.uint8, device=c.device)
+        rc = lib.rvq_codes_pack_bits(c.data_ptr(), n, bits, out.data_ptr(), _stream(c.device))
+    _lib.check(rc, "rvq_codes_pack_bits")
+    return out
+
+
+def unpack_codes(packed: torch.Tensor, shape: tp.Sequence[int], bits: int) -> torch.Tensor:
+    lib = _lib.load()
+    _require_codes(packed, "packed", torch.uint8)
+    n = 1
+    for d in shape:
+        n *= int(d)
+    if packed.numel() != lib.rvq_codes_packed_bytes(n, bits) or not packed.is_contiguous():
+        raise ValueError("packed does not hold that many codes")
+    with torch.cuda.device(packed.device):
+        out = torch.empty(tuple(shape), dtype=torch.int64, device=packed.device)
+        rc = lib.rvq_codes_unpack_bits(packed.data_ptr(), n, bits, out.data_ptr(), _stream(packed.device))
+    _lib.check(rc, "rvq_codes_unpack_bits")
+    return out
+
+
+def stereo_interleave(c0: torch.Tensor, c1: torch.Tensor, per_timestep: bool) -> torch.Tensor:
+    """Two [B, K, T] int64 code tensors (same strides) -> [B, 2K, T] or, per_timestep, [B, K, 2T]."""
+    lib = _lib.load()
+    _require_codes(c0, "codes of channel 0")
+    _require_codes(c1, "codes of channel 1")
+    if c0.shape != c1.shape or c0.dim() != 3:
+        raise ValueError("the two channels must have the same [B, K, T] shape")
+    if c1.stride() != c0.stride():
+        c0, c1 = c0.contiguous(), c1.contiguous()
+    B, K, T = c0.shape
+    dev = c0.device
+    with torch.cuda.device(dev):
+        out = torch.empty((B, K, 2 * T) if per_timestep else (B, 2 * K, T), dtype=torch.int64, device=dev)
+        rc = lib.rvq_stereo_interleave(c0.data_ptr(), c1.data_ptr(), _lib.strides3(c0.stride()), B, K, T,
+                                       1 if per_timestep else 0, out.data_ptr(), _stream(dev))
+    _lib.check(rc, "rvq_stereo_interleave")
+    return out
+
+
+def stereo_split(joint: torch.Tensor, per_timestep: bool) -> tp.Tuple[torch.Tensor, torch.Tensor]:
+    lib = _lib.load()
+    _require_codes(joint, "codes")
+    if joint.dim() != 3 or joint.shape[2 if per_timestep else 1] % 2:
+        raise ValueError("expected [B, 2K, T] codes (or [B, K, 2T] with per_timestep)")
+    j = joint if joint.is_contiguous() else joint.contiguous()
+    B = j.shape[0]
+    K, T = (j.shape[1], j.shape[2] // 2) if per_timestep else (j.shape[1] // 2, j.shape[2])
+    dev = j.device
+    with torch.cuda.device(dev):
+        o0 = torch.empty((B, K, T), dtype=torch.int64, device=dev)
+        o1 = torch.empty((B, K, T), dtype=torch.int64, device=dev)
+        rc = lib.rvq_stereo_split(j.data_ptr(), B, K, T, 1 if per_timestep else 0, o0.data_ptr(), o1.data_ptr(),
+                                  _stream(dev))
+    _lib.check(rc, "rvq_stereo_split")
+    return o0, o1
+
+
+def delay_pattern(seq: torch.Tensor, delays: tp.Sequence[int], offset: int, special: int, out_len: int,
+                  revert: bool, valid_steps: tp.Optional[int] = None
+                  ) -> tp.Tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
+    """build (revert=False): z [B, K, T] -> values [B, K, out_len]; revert: seq [B, K, S] -> values [B, K, out_len].
+    Returns (values, indexes [K, out_len] int64, mask [K, out_len] bool) like the reference's Pattern methods."""
+    lib = _lib.load()
+    _require_codes(seq, "codes")
+    if seq.dim() != 3 or len(delays) != seq.shape[1]:
+        raise ValueError("expected [B, K, L] codes and K delays")
+    B, K, L = seq.shape
+    dev = seq.device
+    d = (ctypes.c_int * K)(*[int(v) for v in delays])
+    with torch.cuda.device(dev):
+        values = torch.empty((B, K, out_len), dtype=torch.int64, device=dev)
+        indexes = torch.empty((K, out_len), dtype=torch.int64, device=dev)
+        mask = torch.empty((K, out_len), dtype=torch.uint8, device=dev)
+        if revert:
+            rc = lib.rvq_delay_revert(seq.data_ptr(), _lib.strides3(seq.stride()), B, K, L,
+                                      L if valid_steps is None else int(valid_steps), out_len, d, int(offset), int(special),
+                                      values.data_ptr(), indexes.data_ptr(), mask.data_ptr(), _stream(dev))
+        else:
+            rc = lib.rvq_delay_build(seq.data_ptr(), _lib.strides3(seq.stride()), B, K, L, out_len, d, int(offset),
+                                     int(special), values.data_ptr(), indexes.data_ptr(), mask.data_ptr(), _stream(dev))
+    _lib.check(rc, "rvq_delay_revert" if revert else "rvq_delay_build")
+    return values, indexes, mask.bool()

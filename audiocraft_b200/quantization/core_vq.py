@@ -329,11 +329,13 @@ class ResidualVectorQuantization(nn.Module):
             _raise_if_bad_codes(self._pack._status)
 
     # -- eval path
-    def encode(self, x: torch.Tensor, n_q: tp.Optional[int] = None) -> torch.Tensor:
-        """[B, D, T] fp32 -> codes [K, B, T] int64 (core_vq.py:387-397)."""
+    def encode(self, x: torch.Tensor, n_q: tp.Optional[int] = None, wire: tp.Optional[torch.Tensor] = None) -> torch.Tensor:
+        """[B, D, T] fp32 -> codes [K, B, T] int64 (core_vq.py:387-397).  `wire` (not in the reference): an int16
+        [K, B, T] view that receives the same codes, for the all-gather of a frame-sharded job (sharded.py)."""
         Ktot, C, _ = self._shape()
         K = n_q or Ktot
-        codes, _ = kernels.encode(x, self._pack.get(self._embeds()), Ktot, C, min(K, Ktot), algo=self.encode_algo)
+        codes, _ = kernels.encode(x, self._pack.get(self._embeds()), Ktot, C, min(K, Ktot), algo=self.encode_algo,
+                                  wire=wire)
         return codes
 
     def decode(self, q_indices: torch.Tensor) -> torch.Tensor:

@@ -8,7 +8,9 @@ frame -- so any split of the B*T frames is valid: no halo, no exchange during co
   * compute:   every rank encodes / decodes its contiguous slice (whole batch items when B >= world,
                else a slice of the time axis)
   * exchange:  one all-gather of the codes per call, as int16 on the wire when bins <= 32767
-               (4x fewer bytes than int64), widened locally.  Quantized latents are not gathered:
+               (4x fewer bytes than int64).  On CUDA the encode kernel writes the int16 copy straight
+               into a preallocated send buffer and one kernel of librvq_b200.so turns the gathered
+               buffer into the [K, B, T] int64 block: two launches per call beside the collective.  Quantized latents are not gathered:
                re-decoding gathered codes locally is cheaper than moving fp32 latents over NVLink.
 """
 from __future__ import annotations
@@ -49,9 +51,14 @@ class ShardedRVQ:
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
         bins = getattr(quantizer, "bins", 1 << 30)
         self.wire_int16 = (bins <= 32767) if wire_int16 is None else wire_int16
+        self._wire_sets: tp.Dict[tuple, dict] = {}
+        self._wired = None
         if self.world > 1 and hasattr(quantizer, "buffers"):
             for buf in quantizer.buffers():
                 dist.broadcast(buf, src=0, group=group)
+            vq = getattr(quantizer, "vq", None)
+            if vq is not None and hasattr(vq, "invalidate_cache"):
+                vq.invalidate_cache()  # the derived codebook pack must be rebuilt from rank 0's buffers
 
     # ---- local pieces -----------------------------------------------------------------------
     def local_slice(self, x: torch.Tensor) -> torch.Tensor:
@@ -61,18 +68,55 @@ class ShardedRVQ:
         lo, hi = shard_bounds(x.shape[axis], self.world, self.rank)
         return x[lo:hi] if axis == 0 else x[:, :, lo:hi]
 
-    def encode_local(self, x_local: torch.Tensor) -> torch.Tensor:
-        return self.q.encode(x_local)
+    def encode_local(self, x_local: torch.Tensor, global_shape: tp.Optional[tp.Tuple[int, int, int]] = None) -> torch.Tensor:
+        """Encodes this rank's slice.  With `global_shape` ([B, D or K, T] of the whole batch) on a CUDA device the
+        encode kernel also writes the codes as int16 straight into the send buffer of the coming all-gather
+        (`rvq_encode_f32_wire`), so `gather_codes` of the returned tensor needs no narrowing pass."""
+        vq = getattr(self.q, "vq", None)
+        if global_shape is None or self.world == 1 or not x_local.is_cuda or not self.wire_int16 or vq is None:
+            return self.q.encode(x_local)
+        B, _, T = global_shape
+        K = self.q.n_q
+        bufs = self._wire_buffers(K, B, T, x_local.device)
+        cur = torch.cuda.current_stream(x_local.device)
+        if bufs["free"] is not None:
+            cur.wait_event(bufs["free"])          # the all-gather that read this send buffer last
+        b_loc, t_loc = x_local.shape[0], x_local.shape[2]
+        wire = bufs["send"][:, :b_loc, :t_loc]
+        codes = vq.encode(x_local, n_q=K, wire=wire).transpose(0, 1)
+        self._wired = (codes, bufs)
+        return codes
 
     def decode_local(self, codes_local: torch.Tensor) -> torch.Tensor:
         return self.q.decode(codes_local)
 
     # ---- exchange ---------------------------------------------------------------------------
+    def _wire_buffers(self, K: int, B: int, T: int, device: torch.device) -> dict:
+        """Send / receive buffers of the int16 all-gather, allocated once per shape, two sets used in turn (the
+        all-gather of one batch runs beside the encode of the next)."""
+        key = (K, B, T, device)
+        sets = self._wire_sets.get(key)
+        if sets is None:
+            axis = shard_axis(B, T, self.world)
+            smax = max(shard_sizes(B if axis == 0 else T, self.world))
+            shape = (K, smax, T) if axis == 0 else (K, B, smax)
+            sets = {"next": 0, "sets": [
+                {"send": torch.zeros(shape, dtype=torch.int16, device=device),
+                 "recv": torch.empty((self.world,) + shape, dtype=torch.int16, device=device),
+                 "free": None, "axis": axis} for _ in range(2)]}
+            self._wire_sets[key] = sets
+        cur = sets["sets"][sets["next"]]
+        sets["next"] ^= 1
+        return cur
+
     def gather_codes(self, codes_local: torch.Tensor, global_shape: tp.Tuple[int, int, int]) -> torch.Tensor:
         """All-gathers per-rank codes [B_r, K, T_r] into the global [B, K, T] (int64) on every rank."""
         B, K, T = global_shape
         if self.world == 1:
             return codes_local
+        if codes_local.is_cuda and self.wire_int16:
+            return self._gather_codes_cuda(codes_local, B, K, T)
+        # host-logic path (CPU tensors under gloo in the tests; int64 on the wire for huge codebooks)
         axis = shard_axis(B, T, self.world)
         sizes = shard_sizes(B if axis == 0 else T, self.world)
         smax = max(sizes)
@@ -94,10 +138,32 @@ class ShardedRVQ:
         full = torch.cat(parts, dim=1 if axis == 0 else 2).to(torch.int64)  # [K, B, T]
         return full.transpose(0, 1)
 
+    def _gather_codes_cuda(self, codes_local: torch.Tensor, B: int, K: int, T: int) -> torch.Tensor:
+        """One all-gather of the int16 send buffer + one widening kernel (`rvq_widen_codes_i16`)."""
+        from . import kernels
+        wired = getattr(self, "_wired", None)
+        if wired is not None and wired[0] is codes_local:
+            bufs = wired[1]                       # the encode kernel already filled the send buffer
+        else:
+            bufs = self._wire_buffers(K, B, T, codes_local.device)
+            cur = torch.cuda.current_stream(codes_local.device)
+            if bufs["free"] is not None:
+                cur.wait_event(bufs["free"])
+            b_loc, t_loc = codes_local.shape[0], codes_local.shape[2]
+            kernels.convert_codes(codes_local, torch.int16, out=bufs["send"][:, :b_loc, :t_loc].transpose(0, 1))
+        self._wired = None
+        dist.all_gather_into_tensor(bufs["recv"].view(torch.uint8).view(-1), bufs["send"].view(torch.uint8).view(-1),
+                                    group=self.group)
+        full = kernels.widen_codes_i16(bufs["recv"], self.world, K, B, T, bufs["axis"])
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream(codes_local.device))
+        bufs["free"] = ev
+        return full.transpose(0, 1)
+
     def gather_codes_async(self, codes_local: torch.Tensor, global_shape: tp.Tuple[int, int, int]):
         """`gather_codes` on a side stream: returns (codes [B, K, T], event).  Nothing in the encode / decode of
-        the next batch depends on the gathered codes, so the all-gather (and the int16 <-> int64 conversions around
-        it) overlaps that work; a consumer calls `torch.cuda.current_stream().wait_event(event)` first."""
+        the next batch depends on the gathered codes, so the all-gather and the widening kernel overlap that work;
+        a consumer calls `torch.cuda.current_stream().wait_event(event)` first."""
         if self.world == 1:
             ev = torch.cuda.Event()
             ev.record()
@@ -106,12 +172,14 @@ class ShardedRVQ:
         if getattr(self, "_gather_stream", None) is None:
             self._gather_stream = torch.cuda.Stream(dev)
         gs = self._gather_stream
-        gs.wait_stream(torch.cuda.current_stream(dev))
+        cur = torch.cuda.current_stream(dev)
+        gs.wait_stream(cur)
         with torch.cuda.stream(gs):
             full = self.gather_codes(codes_local, global_shape)
             codes_local.record_stream(gs)
             ev = torch.cuda.Event()
             ev.record(gs)
+        full.record_stream(cur)  # allocated on the gather stream, consumed on the caller's
         return full, ev
 
     # ---- whole-job calls ----------------------------------------------------------------------
@@ -126,7 +194,8 @@ class ShardedRVQ:
         else:
             B, _, T = x_global_or_local.shape
             x_local = self.local_slice(x_global_or_local)
-        codes_local = self.encode_local(x_local)
+        K = getattr(self.q, "n_q", None)
+        codes_local = self.encode_local(x_local, (B, K, T) if K is not None else None)
         return self.gather_codes(codes_local, (B, codes_local.shape[1], T))
 
     def decode(self, codes_global: torch.Tensor) -> torch.Tensor:

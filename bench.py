@@ -254,6 +254,69 @@ def run_reference_arm(args, rank: int):
 # ------------------------------------------------------------------------------------------------
 # GPU arm
 # ------------------------------------------------------------------------------------------------
+def run_c5_share(dev, rank: int, world: int):
+    """BASELINE.json configs[4]: 2^24 frames (B=8192 x T=2048), n_q=8, bins=2048, sharded by batch items over the
+    ranks, codes all-gathered (int16 on the wire).  Every rank encodes + decodes its share; at N = 1 the share of an
+    8-GPU job (2^21 frames) is timed, without a gather.  Informational extra key, not the bench value."""
+    import torch
+    import torch.distributed as dist
+
+    from audiocraft_b200.quantization import ResidualVectorQuantizer
+    from audiocraft_b200.sharded import ShardedRVQ
+    K5, C5, D5, T5, B5_total = 8, 2048, 128, 2048, 8192
+    ranks = world if world > 1 else 8
+    b_loc = B5_total // ranks
+    torch.manual_seed(5)
+    m5 = ResidualVectorQuantizer(dimension=D5, n_q=K5, bins=C5, kmeans_init=False).to(dev).eval()
+    m5.vq.check_codes = False
+    sh = ShardedRVQ(m5) if world > 1 else None
+    g = torch.Generator(device=dev).manual_seed(4321 + rank)
+    x = torch.randn(b_loc, D5, T5, device=dev, generator=g)
+    gshape = (B5_total, K5, T5)
+
+    def one():
+        codes = sh.encode_local(x, gshape) if sh else m5.encode(x)
+        q = m5.decode(codes)
+        ev = None
+        if sh:
+            _, ev = sh.gather_codes_async(codes, gshape)
+        return q, ev
+
+    with torch.no_grad():
+        for _ in range(2):
+            _, ev = one()
+        if ev is not None:
+            torch.cuda.current_stream(dev).wait_event(ev)
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        reps = 3
+        a.record()
+        for _ in range(reps):
+            _, ev = one()
+        if ev is not None:
+            torch.cuda.current_stream(dev).wait_event(ev)
+        b.record()
+        torch.cuda.synchronize(dev)
+        m5.vq.check_errors()
+    ms = a.elapsed_time(b) / reps
+    t = torch.tensor([ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    frames = b_loc * T5
+    flops = 2.0 * D5 * C5 * K5 * frames
+    del x
+    torch.cuda.empty_cache()
+    return {"workload": "configs[4]: 2^24 frames n_q=8 bins=2048 dim=128 over %d ranks, encode+decode+all-gather of codes" % ranks
+            if world > 1 else "configs[4]: one rank's share at 8 GPUs (2^21 frames), encode+decode, no gather",
+            "frames_per_rank": frames, "ms_per_step": round(ms, 3),
+            "mframes_per_s_aggregate": round(frames * (world if world > 1 else 1) / ms / 1e3, 2),
+            "encode_decode_tflops_per_gpu": round(flops / ms / 1e9, 1)}
+
+
+
 def run_gpu_arm(args, rank: int, world: int, local_rank: int):
     import torch
     import torch.distributed as dist
@@ -279,12 +342,18 @@ def run_gpu_arm(args, rank: int, world: int, local_rank: int):
     g = torch.Generator(device=dev).manual_seed(1234 + rank)
     xs = [torch.randn(B, D, T, device=dev, generator=g) for _ in range(N_ROTATING)]
 
+    gshape = (B * world, K, T)  # every rank contributes one batch of configs[1]: the gathered codes are [B*world, K, T]
+
+    def encode_step(x):
+        # N > 1: the encode kernel also writes the codes as int16 into the send buffer of the all-gather
+        return sharded.encode_local(x, gshape) if world > 1 else m.encode(x)
+
     def step(i):
         x = xs[i % N_ROTATING]
-        codes = m.encode(x)
+        codes = encode_step(x)
         q = m.decode(codes)
         if world > 1:
-            sharded.gather_codes(codes, (B * world, K, T))  # int16 on the wire, widened locally
+            sharded.gather_codes(codes, gshape)  # int16 on the wire, widened by one kernel
         return codes, q
 
     def sync_all():
@@ -296,7 +365,7 @@ def run_gpu_arm(args, rank: int, world: int, local_rank: int):
     # ---- device-resident timing -------------------------------------------------------------
     with torch.no_grad():
         # the sampling thread is started before the warm-up so that its start-up cost is not in the timed region
-        sampler = ClockSampler(local_rank) if rank == 0 else None
+        sampler = ClockSampler(local_rank) if rank == 0 and not os.environ.get("BENCH_NO_SAMPLER") else None
         if sampler:
             sampler.start()
         for i in range(args.warmup):
@@ -310,7 +379,7 @@ def run_gpu_arm(args, rank: int, world: int, local_rank: int):
             step(i)
         sync_all()
         per_step = max((time.perf_counter() - t_w) / 20, 1e-5)
-        extra = torch.tensor([int(min(2000, max(0, 0.06 / per_step)))], device=dev)
+        extra = torch.tensor([int(min(2000, max(0, args.pre_ms * 1e-3 / per_step)))], device=dev)
         if world > 1:
             dist.broadcast(extra, src=0)
         for i in range(int(extra.item())):
@@ -325,13 +394,13 @@ def run_gpu_arm(args, rank: int, world: int, local_rank: int):
         for i in range(args.steps):
             x = xs[i % N_ROTATING]
             ev[i][0].record()
-            codes = m.encode(x)
+            codes = encode_step(x)
             ev[i][1].record()
             q = m.decode(codes)
             ev[i][2].record()
             if world > 1:
                 # on a side stream: the next batch does not depend on the gathered codes
-                _, gathered = sharded.gather_codes_async(codes, (B * world, K, T))
+                _, gathered = sharded.gather_codes_async(codes, gshape)
         if world > 1:
             torch.cuda.current_stream(dev).wait_event(gathered)  # every all-gather ends inside the timed region
         end.record()
@@ -342,12 +411,36 @@ def run_gpu_arm(args, rank: int, world: int, local_rank: int):
         clocks = sampler.stop() if sampler else None
         m.vq.check_errors()
     elapsed_ms = start.elapsed_time(end)
+    log("[bench] per-step encode ms: " + " ".join(f"{e[0].elapsed_time(e[1]):.3f}" for e in ev))
     enc_ms = sum(e[0].elapsed_time(e[1]) for e in ev) / args.steps
     dec_ms = sum(e[1].elapsed_time(e[2]) for e in ev) / args.steps
     t = torch.tensor([elapsed_ms], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     elapsed_ms = float(t.item())
+
+    # ---- N > 1: are the gathered codes right?  (outside the timed region) ---------------------------------------
+    gather_check = None
+    if world > 1:
+        with torch.no_grad():
+            codes0 = encode_step(xs[0])
+            full = sharded.gather_codes(codes0, gshape)          # [B*world, K, T] on every rank
+            torch.cuda.synchronize(dev)
+            if rank == 0:
+                bad = 0
+                for r in range(world):
+                    gr = torch.Generator(device=dev).manual_seed(1234 + r)   # rank r's first input batch, regenerated here
+                    xr = torch.randn(B, D, T, device=dev, generator=gr)
+                    want = m.encode(xr)
+                    bad += int((full[r * B:(r + 1) * B] != want).sum())
+                gather_check = "ok" if bad == 0 else f"FAILED: {bad} codes differ"
+                log(f"[bench] gather_check over {world} ranks: {gather_check}")
+            sync_all()
+
+    # ---- one rank's share of configs[4] (16M frames, n_q=8, strong scaling over the ranks), with its gather ----
+    c5 = None
+    if not args.skip_c5:
+        c5 = run_c5_share(dev, rank, world)
 
     # ---- end to end through the public API with host buffers ---------------------------------
     # audiocraft_b200.host_pipeline.HostPipeline: pinned host latents in, pinned host codes + quantized latents
@@ -467,6 +560,8 @@ def run_gpu_arm(args, rank: int, world: int, local_rank: int):
                     "encode_mframes_per_s": round(frames / enc_ms / 1e3, 3),
                     "decode_mframes_per_s": round(frames / dec_ms / 1e3, 3)},
         "decode_c4": dec_c4,
+        "gather_check": gather_check,
+        "c5_share": c5,
     }
     emit(line)
     if world > 1:
@@ -482,7 +577,9 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--algo", default="", choices=["", "auto", "exact", "tc"])
     ap.add_argument("--skip-cpu", action="store_true")
+    ap.add_argument("--pre-ms", type=float, default=60.0, help="untimed steps before the timed region, in ms of GPU time")
     ap.add_argument("--skip-c4", action="store_true")
+    ap.add_argument("--skip-c5", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     rank = int(os.environ.get("RANK", "0"))

@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define RVQ_B200_ABI_VERSION 1
+#define RVQ_B200_ABI_VERSION 2
 
 #define RVQ_OK 0
 #define RVQ_EINVAL (-1)      /* bad argument (shape, stride, null pointer, size) */
@@ -62,7 +62,8 @@ int rvq_pack_codebooks(const float *const *embed_ptrs, int Ktot, int C, int D, v
  *   codes      device int64 [K][B][T] contiguous -- the torch.stack layout of core_vq.py:396;
  *              the caller returns codes.transpose(0,1) like vq.py:94
  *   quantized  NULL, or device fp32 [B][T][D] contiguous receiving 0.0f + q_0 + ... + q_{K-1}
- *              (eval ResidualVectorQuantization.forward, core_vq.py:363-385)
+ *              (eval ResidualVectorQuantization.forward, core_vq.py:363-385); left untouched when K == 0
+ *              or B*T == 0 (the call returns at once: the caller zero-fills if it wants the empty sum)
  *   workspace  device scratch of rvq_encode_workspace_bytes() bytes, 16-byte aligned (may be NULL when
  *              that is 0).  The tensor-core path keeps the residuals of the frame tiles in flight there
  *              (128 KB per resident CTA, L2 resident); contents need not be preserved between calls,
@@ -72,6 +73,25 @@ int64_t rvq_encode_workspace_bytes(int B, int D, int T, int K, int C, int algo);
 int rvq_encode_f32(const float *x, const int64_t xs[3], int B, int D, int T, const void *pack,
                    int Ktot, int C, int K, int64_t *codes, float *quantized, void *workspace,
                    int64_t workspace_bytes, int algo, void *stream);
+
+/*
+ * rvq_encode_f32 with a second copy of the codes in the wire format of a frame-sharded job (sharded.py; the
+ * reference's path is single-device, SURVEY.md 2a, so this output has no counterpart there): codes16 receives
+ * the same codes as int16, element (k, b, t) at codes16[k * c16s[0] + b * c16s[1] + t].  The strides let every
+ * rank write straight into the send buffer of the all-gather (padded to the largest shard), which removes the
+ * narrowing pass between encode and collective.  Requires C <= 32768.  Everything else as rvq_encode_f32.
+ */
+int rvq_encode_f32_wire(const float *x, const int64_t xs[3], int B, int D, int T, const void *pack,
+                        int Ktot, int C, int K, int64_t *codes, int16_t *codes16, const int64_t c16s[2],
+                        float *quantized, void *workspace, int64_t workspace_bytes, int algo, void *stream);
+
+/*
+ * The other end of that exchange: the all-gathered buffer recv -- W ranks, each [K][smax][T] (axis == 0: the batch
+ * axis is sharded, rank r holds items [lo_r, lo_r + n_r), n_r = B / W + (r < B % W), smax = max n_r) or
+ * [K][B][smax] (axis == 2: the time axis is sharded the same way) -- becomes the int64 [K][B][T] block that
+ * ResidualVectorQuantization.encode returns (core_vq.py:396).  One pass, no intermediate tensors.
+ */
+int rvq_widen_codes_i16(const int16_t *recv, int W, int K, int B, int T, int axis, int64_t *codes, void *stream);
 
 /*
  * rvq_encode_f32 for callers that may not allocate.  No counterpart in the reference.
@@ -89,7 +109,10 @@ int rvq_encode_f32(const float *x, const int64_t xs[3], int B, int D, int T, con
  *     that names the limit.  Only the tensor-core shapes (D == 128, C % 128 == 0, 256 <= C <= 16384) are
  *     accepted: the exact scan (rvq_encode_f32 with RVQ_ALGO_EXACT) needs no workspace in the first place.
  *   - the first call on each device looks up the device address of the built-in array
- *     (cudaGetSymbolAddress) and remembers it; make that first call outside of any stream capture.
+ *     (cudaGetSymbolAddress) and remembers it; it may also be the call that makes the CUDA runtime load the
+ *     library's device code, array included.  Make that first call a warm-up, outside of the request path and
+ *     outside of any stream capture; later calls touch no allocator.  The remembered address does not survive
+ *     cudaDeviceReset.
  *   - all calls on a device share the one array, which keeps the previous call's contents (everything
  *     that has to start from zero is cleared by the call itself): two calls that overlap on the GPU --
  *     different streams, or different host threads -- race on it.  Serialise them on one stream.
@@ -108,11 +131,57 @@ int rvq_encode_f32_static(const float *x, const int64_t xs[3], int B, int D, int
  *              result is physically [B][T][D], i.e. os = {T*D, 1, D}
  *   status     device int64[2], zeroed by the caller before the first use.  An out-of-range code
  *              (the reference raises IndexError) sets status[0] = 1 and status[1] = 1 + the smallest
- *              flat index (b*K + k)*T + t seen; the frame's output for that stage is skipped.
+ *              flat index (b*K + k)*T + t seen; code 0 is used in its place (the output is then not meaningful:
+ *              the host side raises IndexError from the status word).
  */
 int rvq_decode_f32(const void *codes, int code_bytes, const int64_t cs[3], int B, int K, int T,
                    const void *pack, int Ktot, int C, int D, float *out, const int64_t os[3],
                    int64_t *status, void *stream);
+
+/*
+ * Code-stream plumbing after the tokenizer.  Integer index shuffles, one pass each.
+ *
+ * rvq_codes_convert: strided copy between code widths; element (b,k,t) at base[b*s[0] + k*s[1] + t*s[2]]
+ *   (strides in elements), widths 8, 4 or 2 bytes.  The reference's compact cache format is
+ *   `codes.to(torch.int16)` (modules/jasco_conditioners.py:136).
+ * rvq_codes_pack_bits / rvq_codes_unpack_bits: n contiguous int64 codes <-> rvq_codes_packed_bytes(n, bits)
+ *   bytes, `bits` bits per code (11 for 2048 bins), little-endian bit order within groups of 8 codes.
+ *   No counterpart in the reference (it stores int64 or int16).
+ */
+int rvq_codes_convert(const void *src, int src_bytes, const int64_t ss[3], int B, int K, int T, void *dst,
+                      int dst_bytes, const int64_t ds[3], void *stream);
+int64_t rvq_codes_packed_bytes(int64_t n, int bits);
+int rvq_codes_pack_bits(const int64_t *codes, int64_t n, int bits, uint8_t *packed, void *stream);
+int rvq_codes_unpack_bits(const uint8_t *packed, int64_t n, int bits, int64_t *codes, void *stream);
+
+/*
+ * InterleaveStereoCompressionModel.encode / get_left_right_codes (models/encodec.py:474-486):
+ *   per_timestep == 0: joint[b][2k + c][t] = c_c[b][k][t]   ('c b k t -> b (k c) t')
+ *   per_timestep == 1: joint[b][k][2t + c] = c_c[b][k][t]   ('c b k t -> b k (t c)')
+ * c0 / c1: int64, element (b,k,t) at c[b*cs[0] + k*cs[1] + t*cs[2]] (the [B,K,T] views encode returns);
+ * joint and the outputs of rvq_stereo_split are contiguous.
+ */
+int rvq_stereo_interleave(const int64_t *c0, const int64_t *c1, const int64_t cs[3], int B, int K, int T,
+                          int per_timestep, int64_t *joint, void *stream);
+int rvq_stereo_split(const int64_t *joint, int B, int K, int T, int per_timestep, int64_t *c0, int64_t *c1,
+                     void *stream);
+
+/*
+ * Pattern.build_pattern_sequence / revert_pattern_sequence (modules/codebooks_patterns.py:160-183, 224-246) for the
+ * layouts DelayedPatternProvider.get_pattern produces with flatten_first == 0 (:339-356; ParallelPatternProvider is
+ * the all-zero delay case): codebook q appears `offset + delays[q]` steps late, offset = 1 + empty_initial
+ * (0 when the provider omits the special token).
+ *   build:  values[b][q][s] = z[b][q][s - offset - delays[q]] if that timestep is in [0, T) else special
+ *   revert: values[b][q][t] = seq[b][q][t + offset + delays[q]] if that step is in [0, min(S, valid_steps)) else special
+ * z / seq: int64, strided like above; values contiguous [B][K][S] / [B][K][T].  indexes (int64 [K][S] / [K][T]) and
+ * mask (uint8, same shape) are the reference's scatter tables (flattened source index, K*T or K*S where the special
+ * token goes); either may be NULL.  delays: HOST array of K sorted non-negative ints.
+ */
+int rvq_delay_build(const int64_t *z, const int64_t zs[3], int B, int K, int T, int S, const int *delays,
+                    int offset, int64_t special, int64_t *values, int64_t *indexes, uint8_t *mask, void *stream);
+int rvq_delay_revert(const int64_t *seq, const int64_t ss[3], int B, int K, int S, int valid_steps, int T,
+                     const int *delays, int offset, int64_t special, int64_t *values, int64_t *indexes,
+                     uint8_t *mask, void *stream);
 
 /*
  * Diagnostics (no counterpart in the reference): runs the tensor-core encode and also returns, for

@@ -1,0 +1,103 @@
+"""GPU tests of the integer plumbing around the tokenizer (csrc/rvq_codestream.cu), through the C ABI front end.
+
+Integer work: every comparison is exact.  The wire path of a frame-sharded job is emulated on ONE GPU (the driver's
+box has one): each "rank" encodes its shard with the int16 wire output into its part of a gathered buffer, the widening
+kernel must give back the codes of the whole batch.  Stereo interleave and the delay pattern are compared with the
+numpy restatements in oracle/codestream.py, which tests/test_codestream_oracle.py pins against the reference."""
+import numpy as np
+import pytest
+import torch
+
+from audiocraft_b200 import codes as cs
+from audiocraft_b200 import kernels
+from audiocraft_b200.quantization import ResidualVectorQuantizer
+from audiocraft_b200.sharded import shard_bounds, shard_sizes
+from oracle import codestream as ocs
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("B,T,W", [(7, 300, 2), (64, 1500, 8), (1, 1000, 3), (3, 129, 4)])
+def test_wire_encode_and_widen_emulated_ranks(B, T, W):
+    torch.manual_seed(0)
+    m = ResidualVectorQuantizer(dimension=128, n_q=4, bins=2048, kmeans_init=False).cuda().eval()
+    x = torch.randn(B, 128, T, device="cuda")
+    K = 4
+    axis = 0 if B >= W else 2
+    n = B if axis == 0 else T
+    smax = max(shard_sizes(n, W))
+    shape = (K, smax, T) if axis == 0 else (K, B, smax)
+    recv = torch.full((W,) + shape, -7, dtype=torch.int16, device="cuda")
+    with torch.no_grad():
+        whole = m.encode(x)                                            # [B, K, T]
+        for r in range(W):
+            lo, hi = shard_bounds(n, W, r)
+            xr = x[lo:hi] if axis == 0 else x[:, :, lo:hi]
+            wire = recv[r][:, :hi - lo] if axis == 0 else recv[r][:, :, :hi - lo]
+            local = m.vq.encode(xr, n_q=K, wire=wire)                  # [K, b, t]
+            want = whole[lo:hi] if axis == 0 else whole[:, :, lo:hi]
+            assert torch.equal(local.transpose(0, 1), want)
+            assert torch.equal(wire.to(torch.int64), local)
+        full = kernels.widen_codes_i16(recv, W, K, B, T, axis)         # [K, B, T]
+    assert torch.equal(full.transpose(0, 1), whole)
+    # the exact scan writes the wire format too
+    m.vq.encode_algo = "exact"
+    wire = torch.zeros((K, B, T), dtype=torch.int16, device="cuda")
+    with torch.no_grad():
+        local = m.vq.encode(x, n_q=K, wire=wire)
+    assert torch.equal(wire.to(torch.int64), local) and torch.equal(local.transpose(0, 1), whole)
+
+
+def test_convert_and_bit_packing_round_trip():
+    g = torch.Generator(device="cuda").manual_seed(3)
+    codes = torch.randint(0, 2048, (5, 4, 1001), device="cuda", generator=g)
+    view = codes.transpose(0, 1).contiguous().transpose(0, 1)          # the [B, K, T] view encode returns
+    for dt in (torch.int16, torch.int32):
+        small = kernels.convert_codes(view, dt)
+        assert small.dtype == dt and small.is_contiguous() and torch.equal(small.to(torch.int64), codes)
+        assert torch.equal(kernels.convert_codes(small, torch.int64), codes)
+    for bits in (11, 10, 16, 3):
+        c = codes % (1 << bits)
+        packed = kernels.pack_codes(c, bits)
+        assert packed.numel() == (c.numel() * bits + 7) // 8
+        assert np.array_equal(packed.cpu().numpy(), ocs.pack_bits(c.cpu().numpy().reshape(-1), bits))
+        assert torch.equal(kernels.unpack_codes(packed, c.shape, bits), c)
+
+
+@pytest.mark.parametrize("per_timestep", [False, True])
+def test_stereo_interleave_and_split(per_timestep):
+    g = torch.Generator(device="cuda").manual_seed(4)
+    kbt = torch.randint(0, 2048, (2, 4, 3, 257), device="cuda", generator=g)   # [c, K, B, T] blocks as encode writes them
+    c0, c1 = kbt[0].transpose(0, 1), kbt[1].transpose(0, 1)                    # [B, K, T] views
+    joint = cs.interleave_stereo_codes(c0, c1, per_timestep)
+    want = ocs.stereo_interleave(c0.cpu().numpy(), c1.cpu().numpy(), per_timestep)
+    assert np.array_equal(joint.cpu().numpy(), want)
+    l, r = cs.get_left_right_codes(joint, per_timestep)
+    assert torch.equal(l, c0) and torch.equal(r, c1)
+
+
+@pytest.mark.parametrize("K,T,delays,empty_initial", [(4, 50, None, 0), (8, 1500, None, 0), (4, 33, [0, 0, 0, 0], 0),
+                                                       (4, 20, [0, 1, 1, 3], 2), (3, 5, [0, 2, 7], 0)])
+def test_delay_pattern_build_and_revert(K, T, delays, empty_initial):
+    g = torch.Generator(device="cuda").manual_seed(5)
+    z = torch.randint(0, 2048, (3, K, T), device="cuda", generator=g)
+    prov = cs.DelayedPatternProvider(K, delays=delays, empty_initial=empty_initial)
+    pat = prov.get_pattern(T)
+    special = 2048
+    for keep in (False, True):
+        values, indexes, mask = pat.build_pattern_sequence(z, special, keep_only_valid_steps=keep)
+        wv, wi, wm = ocs.delay_build(z.cpu().numpy(), prov.delays, 1 + empty_initial, special, keep)
+        assert np.array_equal(values.cpu().numpy(), wv) and np.array_equal(indexes.cpu().numpy(), wi)
+        assert np.array_equal(mask.cpu().numpy(), wm)
+        back, bi, bm = pat.revert_pattern_sequence(values, special, keep_only_valid_steps=keep)
+        rv, ri, rm = ocs.delay_revert(wv, prov.delays, 1 + empty_initial, special, T, keep)
+        assert np.array_equal(back.cpu().numpy(), rv) and np.array_equal(bi.cpu().numpy(), ri)
+        assert np.array_equal(bm.cpu().numpy(), rm)
+        if not keep:
+            assert torch.equal(back, z)          # the full layout holds every code
+    # a shorter sequence than the pattern (generation in progress): later timesteps come back as the special token
+    values, _, _ = pat.build_pattern_sequence(z, special)
+    part = values[:, :, : values.shape[2] // 2]
+    back, _, bm = pat.revert_pattern_sequence(part, special)
+    rv, _, rm = ocs.delay_revert(part.cpu().numpy(), prov.delays, 1 + empty_initial, special, T, False)
+    assert np.array_equal(back.cpu().numpy(), rv) and np.array_equal(bm.cpu().numpy(), rm)

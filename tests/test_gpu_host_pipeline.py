@@ -36,3 +36,25 @@ def test_host_pipeline_rejects_pageable_or_device_buffers():
     x = torch.randn(2, 128, 8)
     with pytest.raises(ValueError):
         pipe.encode_decode(x, torch.empty(2, 2, 8, dtype=torch.int64).pin_memory(), torch.empty(2, 8, 128).pin_memory())
+
+
+def test_host_pipeline_with_changing_lengths():
+    """Variable-length audio: the staging slots grow once and are reused as views; calls are issued without waiting for
+    the previous one (the pipeline is asynchronous), and every call must still see its own data."""
+    torch.manual_seed(1)
+    m = ResidualVectorQuantizer(dimension=128, n_q=4, bins=2048, kmeans_init=False).cuda().eval()
+    pipe = HostPipeline(m, chunk_items=4)
+    jobs = []
+    for T in (200, 700, 150, 701, 64):
+        x = torch.randn(6, 128, T).pin_memory()
+        codes_h = torch.full((6, 4, T), -1, dtype=torch.int64).pin_memory()
+        quant_h = torch.full((6, T, 128), float("nan")).pin_memory()
+        jobs.append((x, codes_h, quant_h, pipe.encode_decode(x, codes_h, quant_h)))
+    pipe.synchronize()
+    for x, codes_h, quant_h, ev in jobs:
+        ev.synchronize()
+        with torch.no_grad():
+            want = m.encode(x.cuda())
+            want_q = m.decode(want)
+        assert torch.equal(codes_h, want.cpu())
+        assert torch.equal(quant_h, want_q.transpose(1, 2).cpu())

@@ -37,12 +37,18 @@ def _worker(rank, world, port, B, T, out):
         x = torch.randn(B, 128, T, generator=g).to(dev)  # the same global batch on every rank
         with torch.no_grad():
             whole = m.encode(x)                         # single-GPU answer (codebooks are rank 0's by now)
-            local = sh.encode_local(sh.local_slice(x))
+            local = sh.encode_local(sh.local_slice(x))                 # plain encode, narrowed by rvq_codes_convert
             sync = sh.gather_codes(local, (B, 4, T))
             asyn, ev = sh.gather_codes_async(local, (B, 4, T))
             torch.cuda.current_stream(dev).wait_event(ev)
+            wired_ok = True
+            for _ in range(3):                                         # int16 written by the encode kernel; buffers rotate
+                lw = sh.encode_local(sh.local_slice(x), (B, 4, T))
+                fw, ev = sh.gather_codes_async(lw, (B, 4, T))
+                torch.cuda.current_stream(dev).wait_event(ev)
+                wired_ok = wired_ok and bool(torch.equal(fw, whole)) and bool(torch.equal(lw, local))
         torch.cuda.synchronize(dev)
-        out[rank] = (bool(torch.equal(sync, whole)), bool(torch.equal(asyn, whole)), whole[:, :, :8].cpu())
+        out[rank] = (bool(torch.equal(sync, whole)), bool(torch.equal(asyn, whole)) and wired_ok, whole[:, :, :8].cpu())
     finally:
         dist.destroy_process_group()
 

@@ -24,7 +24,7 @@ def test_library_loads_and_exports_every_declared_symbol():
     for name in declared:
         assert hasattr(lib, name), f"{name} declared in include/rvq_b200.h but not exported"
     assert declared == set(_lib.SIGNATURES), "ctypes binding and header disagree"
-    assert _lib.load().rvq_b200_abi_version() == 1
+    assert _lib.load().rvq_b200_abi_version() == _lib.ABI_VERSION == 2
 
 
 def test_pack_bytes_is_host_only_and_validates():

@@ -53,6 +53,30 @@ def test_static_scratch_entry_point_matches_the_workspace_one_twice_in_a_row():
     assert torch.equal(codes, kernels.encode(inputs[0], pack, K, C, K, algo="tc")[0])
 
 
+def test_static_scratch_entry_point_takes_no_device_memory():
+    """What the entry point is for: once the first (warm-up) call on the device has run, a call neither asks the
+    CUDA allocator nor torch's for anything.  Free device memory, as the driver reports it, and torch's own
+    counters must read the same before and after."""
+    lib = _lib.load()
+    pack = _pack()
+    x = torch.from_numpy(gen.normalish(55, (2, D, 500))).cuda()
+    B, _, T = x.shape
+    codes = torch.empty((K, B, T), dtype=torch.int64, device="cuda")
+    quant = torch.empty((B, T, D), device="cuda")
+    args = (x.data_ptr(), _lib.strides3(x.stride()), B, D, T, pack.data_ptr(), K, C, K, codes.data_ptr(), quant.data_ptr(),
+            torch.cuda.current_stream().cuda_stream)
+    assert lib.rvq_encode_f32_static(*args) == 0, _lib.last_error()   # warm-up: module load + symbol look-up
+    torch.cuda.synchronize()
+    free0, _ = torch.cuda.mem_get_info()
+    alloc0, reserved0 = torch.cuda.memory_allocated(), torch.cuda.memory_reserved()
+    for _ in range(3):
+        assert lib.rvq_encode_f32_static(*args) == 0, _lib.last_error()
+    torch.cuda.synchronize()
+    free1, _ = torch.cuda.mem_get_info()
+    assert (torch.cuda.memory_allocated(), torch.cuda.memory_reserved()) == (alloc0, reserved0)
+    assert free1 == free0, f"device memory changed by {free0 - free1} bytes across calls that must not allocate"
+
+
 def test_static_scratch_entry_point_refuses_what_does_not_fit():
     lib = _lib.load()
     pack = _pack()

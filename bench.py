@@ -348,13 +348,26 @@ def run_gpu_arm(args, rank: int, world: int, local_rank: int):
         # N > 1: the encode kernel also writes the codes as int16 into the send buffer of the all-gather
         return sharded.encode_local(x, gshape) if world > 1 else m.encode(x)
 
-    def step(i):
+    class _NoEvent:
+        def record(self):
+            pass
+
+    no_events = [_NoEvent()] * 3
+
+    def step(i, e3=no_events):
+        """One step, the same code (and so the same allocation pattern) untimed and timed: encode, decode, and for
+        N > 1 the all-gather of the codes on a side stream (the next batch does not depend on the gathered codes).
+        Returns the event of the all-gather."""
         x = xs[i % N_ROTATING]
+        e3[0].record()
         codes = encode_step(x)
+        e3[1].record()
         q = m.decode(codes)
+        e3[2].record()
         if world > 1:
-            sharded.gather_codes(codes, gshape)  # int16 on the wire, widened by one kernel
-        return codes, q
+            _, gathered = sharded.gather_codes_async(codes, gshape)  # int16 on the wire, widened by one kernel
+            return gathered
+        return None
 
     def sync_all():
         torch.cuda.synchronize(dev)
@@ -387,24 +400,27 @@ def run_gpu_arm(args, rank: int, world: int, local_rank: int):
         sync_all()
         ev = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(args.steps)]
         start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        # torch creates the CUDA event at its first record(): do that, and the interpreter's garbage collection, outside
+        # of the timed region, so that the host keeps ahead of the GPU from the first timed step on
+        for e3 in ev:
+            for e in e3:
+                e.record()
+        start.record(); end.record()
+        sync_all()
+        import gc
+        gc.collect()
+        gc.disable()
         kernels.launch_count(reset=True)
         if sampler:
             sampler.active = True
         start.record()
         for i in range(args.steps):
-            x = xs[i % N_ROTATING]
-            ev[i][0].record()
-            codes = encode_step(x)
-            ev[i][1].record()
-            q = m.decode(codes)
-            ev[i][2].record()
-            if world > 1:
-                # on a side stream: the next batch does not depend on the gathered codes
-                _, gathered = sharded.gather_codes_async(codes, gshape)
+            gathered = step(i, ev[i])
         if world > 1:
             torch.cuda.current_stream(dev).wait_event(gathered)  # every all-gather ends inside the timed region
         end.record()
         sync_all()
+        gc.enable()
         if sampler:
             sampler.active = False
         launches = kernels.launch_count()

@@ -1,0 +1,179 @@
+// rvq_exchange.cu -- the code exchange of a frame-sharded job without a collective library in the step: every rank
+// stores its int16 codes straight into every peer's receive buffer over NVLink (peer-mapped symmetric memory) and
+// raises a flag there; the widening kernel of each rank waits for the flags of all ranks and turns the gathered
+// buffer into the [K][B][T] int64 block.  Two small launches per step on a side stream, no host round trip, no
+// library kernel that has to find room beside the persistent encode kernel.  (The reference has no multi-GPU path:
+// SURVEY.md 2a; design in SURVEY.md 5 "stretch" and 7.4.)
+//
+// Symmetric buffer of a rank (same layout on every rank, allocated and exchanged by sharded.py):
+//   [0, 4096)                       flags, uint32: data[slot][src rank] at 16 * (slot * W + src),
+//                                   ack[slot][consumer rank] at 2048 / 4 + 16 * (slot * W + consumer)   (64-byte apart)
+//   4096 + slot * slot_bytes + r * shard_bytes   rank r's codes of the step that uses `slot`
+// A step is numbered seq = 1, 2, ... and uses slot seq % nslots.  Flags only grow.
+//   push(seq):  wait until every peer has acknowledged step seq - nslots (it has widened the slot's previous
+//               contents), copy my shard into every rank's slot (mine included), then data[slot][me] = seq everywhere
+//   widen(seq): wait until data[slot][r] >= seq for every r, widen, then ack[slot][me] = seq everywhere
+// Every wait gives up after about 50 ms, records that in the status word (the host raises) and carries on: a lost
+// peer must not hang the GPU.
+#include "rvq_common.cuh"
+
+namespace {
+
+constexpr int MAXW = 16;
+constexpr int TPB = 256;
+constexpr int64_t FLAG_BYTES = 4096;
+constexpr long long TIMEOUT_NS = 50LL * 1000 * 1000;
+
+struct Peers {
+    unsigned char *base[MAXW];  // peer-mapped base address of every rank's symmetric buffer (mine at [rank])
+};
+
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t *p) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_sys(uint32_t *p, uint32_t v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ long long now_ns() {
+    long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+__device__ __forceinline__ uint32_t *data_flag(unsigned char *base, int W, int slot, int src) {
+    return reinterpret_cast<uint32_t *>(base) + 16 * (slot * W + src);
+}
+__device__ __forceinline__ uint32_t *ack_flag(unsigned char *base, int W, int slot, int consumer) {
+    return reinterpret_cast<uint32_t *>(base + 2048) + 16 * (slot * W + consumer);
+}
+// thread p < W of the block waits for flag p; everybody leaves together.  Returns false after a timeout.
+__device__ bool wait_flags(bool acks, unsigned char *mine, int W, int slot, uint32_t want, int64_t *status, int what) {
+    __shared__ int ok;
+    if (threadIdx.x == 0) ok = 1;
+    __syncthreads();
+    if ((int)threadIdx.x < W && want > 0) {
+        const uint32_t *f = acks ? ack_flag(mine, W, slot, (int)threadIdx.x) : data_flag(mine, W, slot, (int)threadIdx.x);
+        const long long t0 = now_ns();
+        while ((int32_t)(ld_acquire_sys(f) - want) < 0) {
+            if (now_ns() - t0 > TIMEOUT_NS) {
+                ok = 0;
+                status[0] = what;                      // 1: push timed out waiting for an ack, 2: widen waiting for data
+                status[1] = (int64_t)threadIdx.x;      // the rank that did not show up
+                break;
+            }
+            __nanosleep(200);
+        }
+    }
+    __syncthreads();
+    return ok != 0;
+}
+
+// the last block to get here (device-scope ticket) runs `f`; every block has fenced its remote stores before
+__device__ __forceinline__ bool last_block(unsigned int *ticket) {
+    __shared__ int last;
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const unsigned int t = atomicAdd(ticket, 1u);
+        last = (t == gridDim.x - 1);
+        if (last) *ticket = 0;
+    }
+    __syncthreads();
+    return last != 0;
+}
+
+__global__ void __launch_bounds__(TPB) push_kernel(Peers peers, int W, int rank, int slot, int nslots, uint32_t seq,
+                                                   int64_t slot_bytes, int64_t shard_bytes, unsigned int *ticket,
+                                                   int64_t *status) {
+    unsigned char *mine = peers.base[rank];
+    wait_flags(true, mine, W, slot, seq > (uint32_t)nslots ? seq - (uint32_t)nslots : 0u, status, 1);
+    const int64_t off = FLAG_BYTES + (int64_t)slot * slot_bytes + (int64_t)rank * shard_bytes;
+    const uint4 *src = reinterpret_cast<const uint4 *>(mine + off);
+    const int64_t n16 = shard_bytes / 16;
+    for (int p = 0; p < W; ++p) {
+        if (p == rank) continue;  // my own shard is already in place: the encode kernel wrote it there
+        uint4 *dst = reinterpret_cast<uint4 *>(peers.base[p] + off);
+        for (int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x; i < n16; i += (int64_t)gridDim.x * TPB) dst[i] = src[i];
+    }
+    if (last_block(ticket) && (int)threadIdx.x < W)
+        st_release_sys(data_flag(peers.base[threadIdx.x], W, slot, rank), seq);
+}
+
+__device__ __forceinline__ void shard_of(int c, int base, int extra, int &r, int &off) {
+    const int big = extra * (base + 1);
+    if (c < big) { r = c / (base + 1); off = c - r * (base + 1); }
+    else { const int d = c - big; r = extra + d / base; off = d - (r - extra) * base; }
+}
+
+__global__ void __launch_bounds__(TPB) widen_wait_kernel(Peers peers, int W, int rank, int slot, uint32_t seq, int64_t slot_bytes,
+                                                         int64_t shard_bytes, int K, int B, int T, int axis,
+                                                         int64_t *__restrict__ out, unsigned int *ticket, int64_t *status) {
+    unsigned char *mine = peers.base[rank];
+    wait_flags(false, mine, W, slot, seq, status, 2);
+    const unsigned char *slot_base = mine + FLAG_BYTES + (int64_t)slot * slot_bytes;
+    const int n = axis == 0 ? B : T, base = n / W, extra = n % W, smax = base + (extra ? 1 : 0);
+    const int64_t total = (int64_t)K * B * T;
+    for (int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x; i < total; i += (int64_t)gridDim.x * TPB) {
+        const int t = (int)(i % T), b = (int)((i / T) % B), k = (int)(i / ((int64_t)T * B));
+        int r, off;
+        int64_t src;
+        if (axis == 0) { shard_of(b, base, extra, r, off); src = ((int64_t)k * smax + off) * T + t; }
+        else { shard_of(t, base, extra, r, off); src = ((int64_t)k * B + b) * smax + off; }
+        out[i] = (int64_t)reinterpret_cast<const int16_t *>(slot_base + (int64_t)r * shard_bytes)[src];
+    }
+    if (last_block(ticket) && (int)threadIdx.x < W)
+        st_release_sys(ack_flag(peers.base[threadIdx.x], W, slot, rank), seq);
+}
+
+int fill_peers(const char *who, void *const *peer_base, int W, int rank, Peers &p) {
+    RVQ_REQUIRE(peer_base && W >= 1 && W <= MAXW && rank >= 0 && rank < W, RVQ_EINVAL, "%s: bad ranks (W=%d rank=%d, at most %d)",
+                who, W, rank, MAXW);
+    for (int i = 0; i < MAXW; ++i) p.base[i] = nullptr;
+    for (int i = 0; i < W; ++i) {
+        RVQ_REQUIRE(peer_base[i] && ((uintptr_t)peer_base[i] & 15) == 0, RVQ_EINVAL, "%s: peer buffer %d is null or unaligned", who, i);
+        p.base[i] = (unsigned char *)peer_base[i];
+    }
+    return RVQ_OK;
+}
+
+}  // namespace
+
+extern "C" int64_t rvq_exchange_header_bytes(void) { return FLAG_BYTES; }
+
+extern "C" int rvq_exchange_push(void *const *peer_base, int W, int rank, int slot, int nslots, uint32_t seq,
+                                 int64_t slot_bytes, int64_t shard_bytes, void *scratch, int64_t *status, void *stream) {
+    Peers p;
+    int rc = fill_peers("rvq_exchange_push", peer_base, W, rank, p);
+    if (rc != RVQ_OK) return rc;
+    RVQ_REQUIRE(nslots >= 1 && slot >= 0 && slot < nslots && nslots * W * 64 <= 2048 && seq >= 1 && shard_bytes > 0 &&
+                    shard_bytes % 16 == 0 && slot_bytes >= (int64_t)W * shard_bytes && slot_bytes % 16 == 0 && scratch && status,
+                RVQ_EINVAL, "rvq_exchange_push: bad slot geometry");
+    const int64_t n16 = shard_bytes / 16;
+    int64_t blocks = (n16 + TPB * 4 - 1) / (TPB * 4);
+    if (blocks > 32) blocks = 32;  // a few SMs' worth: NVLink, not the SMs, carries this
+    if (blocks < 1) blocks = 1;
+    push_kernel<<<(unsigned)blocks, TPB, 0, (cudaStream_t)stream>>>(p, W, rank, slot, nslots, seq, slot_bytes, shard_bytes,
+                                                                   (unsigned int *)scratch, status);
+    rvq_count_launch(1);
+    return rvq_check_launch("rvq_exchange_push");
+}
+
+extern "C" int rvq_exchange_widen(void *const *peer_base, int W, int rank, int slot, int nslots, uint32_t seq,
+                                  int64_t slot_bytes, int64_t shard_bytes, int K, int B, int T, int axis, int64_t *codes,
+                                  void *scratch, int64_t *status, void *stream) {
+    Peers p;
+    int rc = fill_peers("rvq_exchange_widen", peer_base, W, rank, p);
+    if (rc != RVQ_OK) return rc;
+    RVQ_REQUIRE(nslots >= 1 && slot >= 0 && slot < nslots && seq >= 1 && K >= 1 && B >= 1 && T >= 1 && (axis == 0 || axis == 2) &&
+                    codes && scratch && status && (axis == 0 ? B : T) >= W,
+                RVQ_EINVAL, "rvq_exchange_widen: bad arguments");
+    const int64_t total = (int64_t)K * B * T;
+    int64_t blocks = (total + TPB * 8 - 1) / (TPB * 8);
+    if (blocks > 148 * 4) blocks = 148 * 4;
+    if (blocks < 1) blocks = 1;
+    widen_wait_kernel<<<(unsigned)blocks, TPB, 0, (cudaStream_t)stream>>>(p, W, rank, slot, seq, slot_bytes, shard_bytes, K, B, T,
+                                                                         axis, codes, (unsigned int *)scratch + 16, status);
+    rvq_count_launch(1);
+    return rvq_check_launch("rvq_exchange_widen");
+}

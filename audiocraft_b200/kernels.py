@@ -128,13 +128,17 @@ def _require_codes(t: torch.Tensor, what: str, dtype=torch.int64) -> None:
         raise RuntimeError(f"{what} must be {dtype}, got {t.dtype}")
 
 
-def widen_codes_i16(recv: torch.Tensor, W: int, K: int, B: int, T: int, axis: int) -> torch.Tensor:
+def widen_codes_i16(recv: torch.Tensor, W: int, K: int, B: int, T: int, axis: int,
+                    out: tp.Optional[torch.Tensor] = None) -> torch.Tensor:
     """All-gathered int16 codes (W ranks x padded shard, see rvq_widen_codes_i16) -> int64 [K, B, T]."""
     lib = _lib.load()
     _require_codes(recv, "recv", torch.int16)
     dev = recv.device
     with torch.cuda.device(dev):
-        out = torch.empty((K, B, T), dtype=torch.int64, device=dev)
+        if out is None:
+            out = torch.empty((K, B, T), dtype=torch.int64, device=dev)
+        elif out.dtype != torch.int64 or tuple(out.shape) != (K, B, T) or not out.is_contiguous():
+            raise ValueError("out must be a contiguous int64 [K, B, T] tensor")
         rc = lib.rvq_widen_codes_i16(recv.data_ptr(), W, K, B, T, axis, out.data_ptr(), _stream(dev))
     _lib.check(rc, "rvq_widen_codes_i16")
     return out
@@ -253,3 +257,45 @@ def delay_pattern(seq: torch.Tensor, delays: tp.Sequence[int], offset: int, spec
                                      int(special), values.data_ptr(), indexes.data_ptr(), mask.data_ptr(), _stream(dev))
     _lib.check(rc, "rvq_delay_revert" if revert else "rvq_delay_build")
     return values, indexes, mask.bool()
+
+
+# ---- peer-to-peer code exchange (include/rvq_b200.h, csrc/rvq_exchange.cu) ----------------------------------------
+class ExchangeGeometry:
+    """Byte layout of one rank's symmetric exchange buffer for codes [K, B, T] sharded over W ranks."""
+
+    def __init__(self, W: int, K: int, B: int, T: int, nslots: int = 2):
+        lib = _lib.load()
+        self.W, self.K, self.B, self.T, self.nslots = W, K, B, T, nslots
+        self.axis = 0 if B >= W else 2
+        n = B if self.axis == 0 else T
+        self.smax = n // W + (1 if n % W else 0)
+        self.shard_shape = (K, self.smax, T) if self.axis == 0 else (K, B, self.smax)
+        raw = 2 * K * self.smax * (T if self.axis == 0 else B)
+        self.shard_bytes = (raw + 15) // 16 * 16
+        self.slot_bytes = W * self.shard_bytes
+        self.header = int(lib.rvq_exchange_header_bytes())
+        self.total_bytes = self.header + nslots * self.slot_bytes
+
+    def shard_view(self, buf: torch.Tensor, slot: int, rank: int) -> torch.Tensor:
+        """int16 view [K, smax, T] / [K, B, smax] of rank `rank`'s shard of `slot` inside the uint8 buffer `buf`."""
+        off = self.header + slot * self.slot_bytes + rank * self.shard_bytes
+        n = self.shard_shape[0] * self.shard_shape[1] * self.shard_shape[2]
+        return buf[off: off + 2 * n].view(torch.int16).view(self.shard_shape)
+
+
+def exchange_push(geo: ExchangeGeometry, peer_ptrs: tp.Sequence[int], rank: int, seq: int, scratch: torch.Tensor,
+                  status: torch.Tensor, stream: int) -> None:
+    lib = _lib.load()
+    ptrs = (ctypes.c_void_p * geo.W)(*[int(p) for p in peer_ptrs])
+    rc = lib.rvq_exchange_push(ptrs, geo.W, rank, seq % geo.nslots, geo.nslots, seq, geo.slot_bytes, geo.shard_bytes,
+                               scratch.data_ptr(), status.data_ptr(), stream)
+    _lib.check(rc, "rvq_exchange_push")
+
+
+def exchange_widen(geo: ExchangeGeometry, peer_ptrs: tp.Sequence[int], rank: int, seq: int, out: torch.Tensor,
+                   scratch: torch.Tensor, status: torch.Tensor, stream: int) -> None:
+    lib = _lib.load()
+    ptrs = (ctypes.c_void_p * geo.W)(*[int(p) for p in peer_ptrs])
+    rc = lib.rvq_exchange_widen(ptrs, geo.W, rank, seq % geo.nslots, geo.nslots, seq, geo.slot_bytes, geo.shard_bytes,
+                                geo.K, geo.B, geo.T, geo.axis, out.data_ptr(), scratch.data_ptr(), status.data_ptr(), stream)
+    _lib.check(rc, "rvq_exchange_widen")

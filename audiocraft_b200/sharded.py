@@ -44,7 +44,8 @@ class ShardedRVQ:
     Every rank constructs it with its own replica of the module; rank 0's buffers win.
     """
 
-    def __init__(self, quantizer, group: tp.Optional[dist.ProcessGroup] = None, wire_int16: tp.Optional[bool] = None):
+    def __init__(self, quantizer, group: tp.Optional[dist.ProcessGroup] = None, wire_int16: tp.Optional[bool] = None,
+                 exchange: str = "auto"):
         self.q = quantizer
         self.group = group
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
@@ -53,6 +54,11 @@ class ShardedRVQ:
         self.wire_int16 = (bins <= 32767) if wire_int16 is None else wire_int16
         self._wire_sets: tp.Dict[tuple, dict] = {}
         self._wired = None
+        # "p2p": peer stores over NVLink into symmetric memory + flags (csrc/rvq_exchange.cu); "nccl": all_gather;
+        # "auto": p2p when torch's symmetric memory can be set up for the group, else nccl
+        assert exchange in ("auto", "p2p", "nccl")
+        self.exchange = exchange
+        self._p2p: tp.Dict[tuple, tp.Any] = {}
         if self.world > 1 and hasattr(quantizer, "buffers"):
             for buf in quantizer.buffers():
                 dist.broadcast(buf, src=0, group=group)
@@ -95,6 +101,14 @@ class ShardedRVQ:
         """Send / receive buffers of the int16 all-gather, allocated once per shape, two sets used in turn (the
         all-gather of one batch runs beside the encode of the next)."""
         key = (K, B, T, device)
+        p2p = self._p2p_state(K, B, T, device)
+        if p2p is not None:
+            p2p["seq"] += 1
+            seq = p2p["seq"]
+            geo = p2p["geo"]
+            # "free": my push and widen of the step that used this slot last (they read my shard of the slot)
+            return {"send": geo.shard_view(p2p["buf"], seq % geo.nslots, self.rank), "free": p2p["free"][seq % geo.nslots],
+                    "axis": geo.axis, "p2p": p2p, "seq": seq}
         sets = self._wire_sets.get(key)
         if sets is None:
             axis = shard_axis(B, T, self.world)
@@ -108,6 +122,48 @@ class ShardedRVQ:
         cur = sets["sets"][sets["next"]]
         sets["next"] ^= 1
         return cur
+
+    def _p2p_state(self, K: int, B: int, T: int, device: torch.device):
+        """Symmetric exchange buffer for this shape (allocated and rendezvoused once, collectively), or None."""
+        if self.exchange == "nccl" or self.world == 1 or device.type != "cuda" or not self.wire_int16:
+            return None
+        key = (K, B, T, device)
+        if key in self._p2p:
+            return self._p2p[key]
+        from . import kernels
+        state = None
+        try:
+            import torch.distributed._symmetric_memory as symm_mem
+            geo = kernels.ExchangeGeometry(self.world, K, B, T, nslots=2)
+            buf = symm_mem.empty(geo.total_bytes, dtype=torch.uint8, device=device)
+            hdl = symm_mem.rendezvous(buf, self.group if self.group is not None else dist.group.WORLD)
+            buf.zero_()
+            torch.cuda.synchronize(device)
+            dist.barrier(group=self.group)     # nobody pushes into a buffer that is still being cleared
+            state = {"geo": geo, "buf": buf, "hdl": hdl, "ptrs": [int(p) for p in hdl.buffer_ptrs], "seq": 0, "free": [None, None],
+                     "scratch": torch.zeros(256, dtype=torch.uint8, device=device),
+                     "status": torch.zeros(2, dtype=torch.int64, device=device)}
+        except Exception as e:  # symmetric memory not available for this group / driver
+            if self.exchange == "p2p":
+                raise
+            import warnings
+            warnings.warn(f"symmetric memory unavailable ({e}); the codes are exchanged with NCCL all_gather")
+        # every rank must take the same path: agree
+        flag = torch.tensor([1 if state is not None else 0], device=device)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=self.group)
+        if int(flag.item()) == 0:
+            state = None
+        self._p2p[key] = state
+        return state
+
+    def check_exchange(self) -> None:
+        """Raises if a wait of the peer-to-peer exchange timed out since the last check (a rank did not show up)."""
+        for st in self._p2p.values():
+            if st is not None:
+                what, who = st["status"].tolist()
+                if what:
+                    st["status"].zero_()
+                    raise RuntimeError(f"code exchange: {'push' if what == 1 else 'widen'} timed out waiting for rank {who}")
 
     def gather_codes(self, codes_local: torch.Tensor, global_shape: tp.Tuple[int, int, int]) -> torch.Tensor:
         """All-gathers per-rank codes [B_r, K, T_r] into the global [B, K, T] (int64) on every rank."""
@@ -138,7 +194,8 @@ class ShardedRVQ:
         full = torch.cat(parts, dim=1 if axis == 0 else 2).to(torch.int64)  # [K, B, T]
         return full.transpose(0, 1)
 
-    def _gather_codes_cuda(self, codes_local: torch.Tensor, B: int, K: int, T: int) -> torch.Tensor:
+    def _gather_codes_cuda(self, codes_local: torch.Tensor, B: int, K: int, T: int,
+                           out: tp.Optional[torch.Tensor] = None) -> torch.Tensor:
         """One all-gather of the int16 send buffer + one widening kernel (`rvq_widen_codes_i16`)."""
         from . import kernels
         wired = getattr(self, "_wired", None)
@@ -152,9 +209,21 @@ class ShardedRVQ:
             b_loc, t_loc = codes_local.shape[0], codes_local.shape[2]
             kernels.convert_codes(codes_local, torch.int16, out=bufs["send"][:, :b_loc, :t_loc].transpose(0, 1))
         self._wired = None
+        if "p2p" in bufs:
+            st = bufs["p2p"]
+            dev = codes_local.device
+            if out is None:
+                out = torch.empty((K, B, T), dtype=torch.int64, device=dev)
+            stream = torch.cuda.current_stream(dev).cuda_stream
+            kernels.exchange_push(st["geo"], st["ptrs"], self.rank, bufs["seq"], st["scratch"], st["status"], stream)
+            kernels.exchange_widen(st["geo"], st["ptrs"], self.rank, bufs["seq"], out, st["scratch"], st["status"], stream)
+            ev = torch.cuda.Event()
+            ev.record(torch.cuda.current_stream(dev))
+            st["free"][bufs["seq"] % st["geo"].nslots] = ev
+            return out.transpose(0, 1)
         dist.all_gather_into_tensor(bufs["recv"].view(torch.uint8).view(-1), bufs["send"].view(torch.uint8).view(-1),
                                     group=self.group)
-        full = kernels.widen_codes_i16(bufs["recv"], self.world, K, B, T, bufs["axis"])
+        full = kernels.widen_codes_i16(bufs["recv"], self.world, K, B, T, bufs["axis"], out=out)
         ev = torch.cuda.Event()
         ev.record(torch.cuda.current_stream(codes_local.device))
         bufs["free"] = ev
@@ -173,13 +242,23 @@ class ShardedRVQ:
             self._gather_stream = torch.cuda.Stream(dev)
         gs = self._gather_stream
         cur = torch.cuda.current_stream(dev)
+        B, K, T = global_shape
+        fast = codes_local.is_cuda and self.wire_int16
+        wired = fast and self._wired is not None and self._wired[0] is codes_local
+        # the result is allocated on the caller's stream (its pool is the warm one) and filled on the gather stream
+        out = torch.empty((K, B, T), dtype=torch.int64, device=dev) if fast else None
         gs.wait_stream(cur)
         with torch.cuda.stream(gs):
-            full = self.gather_codes(codes_local, global_shape)
-            codes_local.record_stream(gs)
+            if fast:
+                full = self._gather_codes_cuda(codes_local, B, K, T, out=out)
+                out.record_stream(gs)
+            else:
+                full = self.gather_codes(codes_local, global_shape)
+                full.record_stream(cur)
+            if not wired:
+                codes_local.record_stream(gs)  # read on the gather stream (the wired path reads the send buffer only)
             ev = torch.cuda.Event()
             ev.record(gs)
-        full.record_stream(cur)  # allocated on the gather stream, consumed on the caller's
         return full, ev
 
     # ---- whole-job calls ----------------------------------------------------------------------

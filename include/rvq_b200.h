@@ -94,6 +94,26 @@ int rvq_encode_f32_wire(const float *x, const int64_t xs[3], int B, int D, int T
 int rvq_widen_codes_i16(const int16_t *recv, int W, int K, int B, int T, int axis, int64_t *codes, void *stream);
 
 /*
+ * The same exchange without a collective library in the step (no counterpart in the reference): every rank owns a
+ * "symmetric" buffer that its peers can address (sharded.py allocates it with torch's symmetric memory and passes
+ * the W peer-mapped base addresses as a HOST array).  Layout: rvq_exchange_header_bytes() of flags, then `nslots`
+ * slots of `slot_bytes`, each holding W shards of `shard_bytes` (rank r's int16 codes [K][smax][T] or [K][B][smax],
+ * padded to a multiple of 16 bytes).  Step seq = 1, 2, ... uses slot seq % nslots; the encode kernel writes this
+ * rank's shard of the slot directly (rvq_encode_f32_wire).
+ *   rvq_exchange_push   stores this rank's shard into every peer's slot over NVLink and raises this rank's data flag
+ *                       there (after waiting, for seq > nslots, until every peer has consumed step seq - nslots)
+ *   rvq_exchange_widen  waits for the data flags of all ranks, writes codes int64 [K][B][T], acknowledges the slot
+ * scratch: 256 zeroed device bytes private to the caller; status: device int64[2], zeroed; a wait that lasts longer
+ * than 50 ms writes status[0] = 1 (push) / 2 (widen) and status[1] = the rank waited for, and the kernel carries on.
+ */
+int64_t rvq_exchange_header_bytes(void);
+int rvq_exchange_push(void *const *peer_base, int W, int rank, int slot, int nslots, uint32_t seq,
+                      int64_t slot_bytes, int64_t shard_bytes, void *scratch, int64_t *status, void *stream);
+int rvq_exchange_widen(void *const *peer_base, int W, int rank, int slot, int nslots, uint32_t seq,
+                       int64_t slot_bytes, int64_t shard_bytes, int K, int B, int T, int axis, int64_t *codes,
+                       void *scratch, int64_t *status, void *stream);
+
+/*
  * rvq_encode_f32 for callers that may not allocate.  No counterpart in the reference.
  *
  * rvq_encode_f32 needs a workspace (the residuals and remembered scores of the frame tiles in flight), which

@@ -101,3 +101,50 @@ def test_delay_pattern_build_and_revert(K, T, delays, empty_initial):
     back, _, bm = pat.revert_pattern_sequence(part, special)
     rv, _, rm = ocs.delay_revert(part.cpu().numpy(), prov.delays, 1 + empty_initial, special, T, False)
     assert np.array_equal(back.cpu().numpy(), rv) and np.array_equal(bm.cpu().numpy(), rm)
+
+
+@pytest.mark.parametrize("B,T,W", [(7, 300, 2), (16, 700, 8), (2, 1000, 3)])
+def test_peer_exchange_emulated_ranks(B, T, W):
+    """The NVLink exchange (rvq_exchange_push / rvq_exchange_widen) with W ranks emulated on one GPU: W plain device
+    buffers stand in for the peers' symmetric buffers, the ranks' kernels run one after the other on one stream (every
+    flag a kernel waits for is already set when it starts).  Five steps, two slots: slots and flags are reused."""
+    torch.manual_seed(0)
+    K = 4
+    m = ResidualVectorQuantizer(dimension=128, n_q=K, bins=2048, kmeans_init=False).cuda().eval()
+    geo = kernels.ExchangeGeometry(W, K, B, T, nslots=2)
+    bufs = [torch.zeros(geo.total_bytes, dtype=torch.uint8, device="cuda") for _ in range(W)]
+    ptrs = [b.data_ptr() for b in bufs]
+    scratch = [torch.zeros(256, dtype=torch.uint8, device="cuda") for _ in range(W)]
+    status = [torch.zeros(2, dtype=torch.int64, device="cuda") for _ in range(W)]
+    st = torch.cuda.current_stream().cuda_stream
+    n = B if geo.axis == 0 else T
+    for seq in range(1, 6):
+        x = torch.randn(B, 128, T, device="cuda")
+        with torch.no_grad():
+            whole = m.encode(x)
+            for r in range(W):
+                lo, hi = shard_bounds(n, W, r)
+                xr = x[lo:hi] if geo.axis == 0 else x[:, :, lo:hi]
+                shard = geo.shard_view(bufs[r], seq % 2, r)
+                wire = shard[:, :hi - lo] if geo.axis == 0 else shard[:, :, :hi - lo]
+                m.vq.encode(xr, n_q=K, wire=wire)
+            for r in range(W):
+                kernels.exchange_push(geo, ptrs, r, seq, scratch[r], status[r], st)
+            for r in range(W):
+                out = torch.empty((K, B, T), dtype=torch.int64, device="cuda")
+                kernels.exchange_widen(geo, ptrs, r, seq, out, scratch[r], status[r], st)
+                assert torch.equal(out.transpose(0, 1), whole), f"step {seq}, rank {r}"
+    for r in range(W):
+        assert status[r].tolist() == [0, 0]
+
+
+def test_peer_exchange_wait_times_out_instead_of_hanging():
+    """A rank whose peers never push: the widening kernel gives up after about 50 ms and says whom it waited for."""
+    geo = kernels.ExchangeGeometry(2, 4, 4, 64, nslots=2)
+    bufs = [torch.zeros(geo.total_bytes, dtype=torch.uint8, device="cuda") for _ in range(2)]
+    scratch = torch.zeros(256, dtype=torch.uint8, device="cuda")
+    status = torch.zeros(2, dtype=torch.int64, device="cuda")
+    out = torch.empty((4, 4, 64), dtype=torch.int64, device="cuda")
+    kernels.exchange_widen(geo, [b.data_ptr() for b in bufs], 0, 1, out, scratch, status, torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    assert status[0].item() == 2 and status[1].item() in (0, 1)

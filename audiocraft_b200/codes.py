@@ -137,3 +137,19 @@ class ParallelPatternProvider(DelayedPatternProvider):
 
     def __init__(self, n_q: int, empty_initial: int = 0):
         super().__init__(n_q, [0] * n_q, empty_initial=empty_initial)
+
+
+def decode_pattern_sequence(quantizer, seq: torch.Tensor, pattern: Pattern) -> torch.Tensor:
+    """`quantizer.decode(pattern.revert_pattern_sequence(seq, ...)[0])` in one kernel launch: the gather reads the
+    language model's delayed [B, K, S] tokens in place (rvq_decode_delayed_f32).  `seq` must hold every step of the
+    pattern's `timesteps` frames (S >= offset + timesteps + max_delay); returns [B, D, T] like `decode`."""
+    vq = quantizer.vq
+    Ktot, C, D = vq._shape()
+    B, K, S = seq.shape
+    assert K == pattern.n_q
+    late = [pattern.offset + d for d in pattern.delays]
+    status = vq._pack.status(seq.device)
+    out = kernels.decode(seq, vq._pack.get(vq._embeds()), Ktot, C, D, status, steps_late=late, frames=pattern.timesteps)
+    if vq.check_codes:
+        vq.check_errors()
+    return out.transpose(1, 2)

@@ -31,17 +31,38 @@ __device__ __noinline__ void rvq_flag_bad_code(int64_t *status, long long flat) 
 // DCH = D / 128 when D is 128/256/512 (unrolled), else 0 -> generic chunk loop.
 // Dynamic shared memory: int32 codes [warps][32 frames][KP] of the 32 frames a warp is working
 // on; an out-of-range code is reported through `status` and replaced by 0.
-template <typename CodeT, int KT, int DCH>
+// STAGED: the K codebooks are copied into shared memory first and every row comes from there (small models only:
+// K*C*D*4 bytes must fit beside the codes; the debug model's 4 x 400 x 32 x 4 = 205 KB does).
+// koff: per-stage extra offset (in elements) into `codes`: a delayed pattern is read in place (stage k's code of
+// frame t sits koff.v[k] / cs_t steps later in the sequence, codebooks_patterns.py:339-356).
+struct RvqStageOffsets { int64_t v[RVQ_MAX_STAGES]; };
+
+template <bool STAGED>
+__device__ __forceinline__ float4 load_row(const char *p) {
+    if (STAGED) return *reinterpret_cast<const float4 *>(p);
+    return __ldg(reinterpret_cast<const float4 *>(p));
+}
+
+template <typename CodeT, int KT, int DCH, bool STAGED>
 __global__ void __launch_bounds__(256)
 rvq_decode_kernel(const void *__restrict__ codes, int64_t cs_b, int64_t cs_k, int64_t cs_t, int B, int K, int T,
-                  const float *__restrict__ embed, int C, int D, float *__restrict__ out, int64_t os_b,
-                  int64_t os_d, int64_t os_t, int64_t *__restrict__ status) {
-    extern __shared__ int s_codes[];
+                  const float *__restrict__ embed_g, int C, int D, float *__restrict__ out, int64_t os_b,
+                  int64_t os_d, int64_t os_t, int64_t *__restrict__ status, const RvqStageOffsets koff) {
+    extern __shared__ __align__(16) int s_codes[];
+    const float *embed = embed_g;
+    if (STAGED) {
+        // codebooks first (16-byte aligned at the start of dynamic shared memory), the warps' code areas after them
+        float4 *cb = reinterpret_cast<float4 *>(s_codes);
+        const int64_t n4 = (int64_t)K * C * D / 4;
+        for (int64_t i = threadIdx.x; i < n4; i += blockDim.x) cb[i] = __ldg(reinterpret_cast<const float4 *>(embed_g) + i);
+        __syncthreads();
+        embed = reinterpret_cast<const float *>(cb);
+    }
     const int lane = threadIdx.x & 31;
     const int wib = threadIdx.x >> 5;
     const int warps_per_block = blockDim.x >> 5;
     const int KP = KT > 0 ? ((KT + 3) & ~3) : ((K + 3) & ~3);  // codes per frame in smem, padded to 4
-    int *wcodes = s_codes + (size_t)wib * KP * 32;
+    int *wcodes = s_codes + (STAGED ? (size_t)K * C * D : 0) + (size_t)wib * KP * 32;
     const int64_t tblocks = (T + 31) / 32;  // 32-frame groups per batch item
     const int64_t ngroups = (int64_t)B * tblocks;
     const int nchunks = DCH > 0 ? DCH : (D + 127) / 128;
@@ -61,7 +82,7 @@ rvq_decode_kernel(const void *__restrict__ codes, int64_t cs_b, int64_t cs_k, in
 #pragma unroll
             for (int k = 0; k < (KT > 0 ? KT : 1); ++k) {
                 for (int kk = k; kk < Kc; kk += (KT > 0 ? KT : 1)) {
-                    long long c = load_code<CodeT>(codes, base + kk * cs_k);
+                    long long c = load_code<CodeT>(codes, base + kk * cs_k + koff.v[kk]);
                     if (c < 0 || c >= C) {
                         rvq_flag_bad_code(status, (b * K + kk) * (long long)T + t0 + lane);
                         c = 0;
@@ -95,8 +116,8 @@ rvq_decode_kernel(const void *__restrict__ codes, int64_t cs_b, int64_t cs_k, in
                     float4 row[8];
 #pragma unroll
                     for (int j = 0; j < KT; ++j)
-                        row[j] = __ldg(reinterpret_cast<const float4 *>(
-                            ebase + (size_t)((uint32_t)j * stage_stride + (uint32_t)code[j] * (uint32_t)D) * 4u));
+                        row[j] = load_row<STAGED>(
+                            ebase + (size_t)((uint32_t)j * stage_stride + (uint32_t)code[j] * (uint32_t)D) * 4u);
 #pragma unroll
                     for (int j = 0; j < KT; ++j) {  // stage order (core_vq.py:401-404)
                         acc.x = __fadd_rn(acc.x, row[j].x);
@@ -111,8 +132,8 @@ rvq_decode_kernel(const void *__restrict__ codes, int64_t cs_b, int64_t cs_k, in
                         for (int j = 0; j < 8; ++j) {
                             row[j] = make_float4(0.f, 0.f, 0.f, 0.f);
                             if (k0 + j < K)
-                                row[j] = __ldg(reinterpret_cast<const float4 *>(
-                                    ebase + ((size_t)(k0 + j) * stage_stride + (size_t)fc[k0 + j] * D) * 4u));
+                                row[j] = load_row<STAGED>(
+                                    ebase + ((size_t)(k0 + j) * stage_stride + (size_t)fc[k0 + j] * D) * 4u);
                         }
 #pragma unroll
                         for (int j = 0; j < 8; ++j) {
@@ -139,21 +160,36 @@ rvq_decode_kernel(const void *__restrict__ codes, int64_t cs_b, int64_t cs_k, in
 
 template <typename CodeT, int KT>
 static int launch_decode_k(const void *codes, const int64_t cs[3], int B, int K, int T, const RvqPackView &pv,
-                           float *out, const int64_t os[3], int64_t *status, cudaStream_t stream) {
+                           float *out, const int64_t os[3], int64_t *status, const RvqStageOffsets &koff,
+                           cudaStream_t stream) {
     const int64_t ngroups = (int64_t)B * ((T + 31) / 32);
     int dev = 0, sms = 148;
     RVQ_CUDA(cudaGetDevice(&dev));
     RVQ_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     const int KP = (K + 3) & ~3;
     const int wpb = KP <= 32 ? 8 : 4;
-    const size_t smem = (size_t)wpb * KP * 32 * sizeof(int);
+    const size_t smem_codes = (size_t)wpb * KP * 32 * sizeof(int);
     int64_t blocks = (ngroups + wpb - 1) / wpb;
-    const int64_t cap = (int64_t)sms * 8 * 8;  // grid-stride beyond a few waves of resident CTAs
+    // Small models: all K codebooks in shared memory, one persistent CTA per SM, when there are enough frames to
+    // pay for the copy (each CTA reads the codebooks once from L2).
+    const size_t cb_bytes = (size_t)K * pv.C * pv.D * sizeof(float);
+    const bool staged = cb_bytes + smem_codes <= 220 * 1024 && ngroups * 32 >= 64 * (int64_t)K * pv.C;
+    const size_t smem = smem_codes + (staged ? cb_bytes : 0);
+    const int64_t cap = staged ? (int64_t)sms : (int64_t)sms * 8 * 8;  // grid-stride beyond a few waves of resident CTAs
     if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
-#define RVQ_DEC_LAUNCH(DCH)                                                                              \
-    rvq_decode_kernel<CodeT, KT, DCH><<<(unsigned)blocks, wpb * 32, smem, stream>>>(                     \
-        codes, cs[0], cs[1], cs[2], B, K, T, pv.embed, pv.C, pv.D, out, os[0], os[1], os[2], status)
+#define RVQ_DEC_LAUNCH(DCH)                                                                                       \
+    do {                                                                                                          \
+        if (staged) {                                                                                             \
+            auto kern = rvq_decode_kernel<CodeT, KT, DCH, true>;                                                  \
+            RVQ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));          \
+            kern<<<(unsigned)blocks, wpb * 32, smem, stream>>>(codes, cs[0], cs[1], cs[2], B, K, T, pv.embed, pv.C, \
+                                                               pv.D, out, os[0], os[1], os[2], status, koff);      \
+        } else {                                                                                                  \
+            rvq_decode_kernel<CodeT, KT, DCH, false><<<(unsigned)blocks, wpb * 32, smem, stream>>>(                \
+                codes, cs[0], cs[1], cs[2], B, K, T, pv.embed, pv.C, pv.D, out, os[0], os[1], os[2], status, koff); \
+        }                                                                                                         \
+    } while (0)
     if (pv.D == 128) RVQ_DEC_LAUNCH(1);
     else if (pv.D == 256) RVQ_DEC_LAUNCH(2);
     else if (pv.D == 512) RVQ_DEC_LAUNCH(4);
@@ -165,15 +201,16 @@ static int launch_decode_k(const void *codes, const int64_t cs[3], int B, int K,
 
 template <typename CodeT>
 static int launch_decode(const void *codes, const int64_t cs[3], int B, int K, int T, const RvqPackView &pv,
-                         float *out, const int64_t os[3], int64_t *status, cudaStream_t stream) {
+                         float *out, const int64_t os[3], int64_t *status, const RvqStageOffsets &koff,
+                         cudaStream_t stream) {
     switch (K) {
-        case 1: return launch_decode_k<CodeT, 1>(codes, cs, B, K, T, pv, out, os, status, stream);
-        case 2: return launch_decode_k<CodeT, 2>(codes, cs, B, K, T, pv, out, os, status, stream);
-        case 3: return launch_decode_k<CodeT, 3>(codes, cs, B, K, T, pv, out, os, status, stream);
-        case 4: return launch_decode_k<CodeT, 4>(codes, cs, B, K, T, pv, out, os, status, stream);
-        case 6: return launch_decode_k<CodeT, 6>(codes, cs, B, K, T, pv, out, os, status, stream);
-        case 8: return launch_decode_k<CodeT, 8>(codes, cs, B, K, T, pv, out, os, status, stream);
-        default: return launch_decode_k<CodeT, 0>(codes, cs, B, K, T, pv, out, os, status, stream);
+        case 1: return launch_decode_k<CodeT, 1>(codes, cs, B, K, T, pv, out, os, status, koff, stream);
+        case 2: return launch_decode_k<CodeT, 2>(codes, cs, B, K, T, pv, out, os, status, koff, stream);
+        case 3: return launch_decode_k<CodeT, 3>(codes, cs, B, K, T, pv, out, os, status, koff, stream);
+        case 4: return launch_decode_k<CodeT, 4>(codes, cs, B, K, T, pv, out, os, status, koff, stream);
+        case 6: return launch_decode_k<CodeT, 6>(codes, cs, B, K, T, pv, out, os, status, koff, stream);
+        case 8: return launch_decode_k<CodeT, 8>(codes, cs, B, K, T, pv, out, os, status, koff, stream);
+        default: return launch_decode_k<CodeT, 0>(codes, cs, B, K, T, pv, out, os, status, koff, stream);
     }
 }
 
@@ -183,7 +220,9 @@ int rvq_decode_launch_internal(const int64_t *codes_kbt, int B, int K, int T, co
                                int64_t *status, cudaStream_t stream) {
     const int64_t cs[3] = {(int64_t)T, (int64_t)B * T, 1};
     const int64_t os[3] = {(int64_t)T * pv.D, 1, (int64_t)pv.D};
-    return launch_decode<long long>(codes_kbt, cs, B, K, T, pv, out, os, status, stream);
+    RvqStageOffsets koff;
+    for (int k = 0; k < RVQ_MAX_STAGES; ++k) koff.v[k] = 0;
+    return launch_decode<long long>(codes_kbt, cs, B, K, T, pv, out, os, status, koff, stream);
 }
 
 // K == 0: the reference returns the scalar 0.0; the wrapper never calls with K == 0 on a
@@ -197,20 +236,19 @@ __global__ void rvq_fill_zero_kernel(float *__restrict__ out, int64_t os_b, int6
     out[b * os_b + d * os_d + t * os_t] = 0.0f;
 }
 
-extern "C" int rvq_decode_f32(const void *codes, int code_bytes, const int64_t cs[3], int B, int K, int T,
-                              const void *pack, int Ktot, int C, int D, float *out, const int64_t os[3],
-                              int64_t *status, void *stream_) {
-    cudaStream_t stream = (cudaStream_t)stream_;
-    RVQ_REQUIRE(B >= 0 && K >= 0 && T >= 0, RVQ_EINVAL, "rvq_decode_f32: negative size");
+static int decode_common(const char *who, const void *codes, int code_bytes, const int64_t cs[3], int B, int K, int T,
+                         const void *pack, int Ktot, int C, int D, float *out, const int64_t os[3], int64_t *status,
+                         const int *steps_late, cudaStream_t stream) {
+    RVQ_REQUIRE(B >= 0 && K >= 0 && T >= 0, RVQ_EINVAL, "%s: negative size", who);
     if ((int64_t)B * T == 0) return RVQ_OK;
-    RVQ_REQUIRE(pack && out && os && status, RVQ_EINVAL, "rvq_decode_f32: null pointer");
-    RVQ_REQUIRE(Ktot > 0 && Ktot <= RVQ_MAX_STAGES && C > 0 && D > 0, RVQ_EINVAL, "rvq_decode_f32: bad pack sizes");
-    RVQ_REQUIRE(K <= Ktot, RVQ_EINVAL, "rvq_decode_f32: %d code streams but only %d codebooks", K, Ktot);
-    RVQ_REQUIRE(D % 4 == 0, RVQ_EUNSUPPORTED, "rvq_decode_f32: dimension %d is not a multiple of 4", D);
+    RVQ_REQUIRE(pack && out && os && status, RVQ_EINVAL, "%s: null pointer", who);
+    RVQ_REQUIRE(Ktot > 0 && Ktot <= RVQ_MAX_STAGES && C > 0 && D > 0, RVQ_EINVAL, "%s: bad pack sizes", who);
+    RVQ_REQUIRE(K <= Ktot, RVQ_EINVAL, "%s: %d code streams but only %d codebooks", who, K, Ktot);
+    RVQ_REQUIRE(D % 4 == 0, RVQ_EUNSUPPORTED, "%s: dimension %d is not a multiple of 4", who, D);
     RVQ_REQUIRE(os[1] != 1 || (((uintptr_t)out & 15) == 0 && os[0] % 4 == 0 && os[2] % 4 == 0), RVQ_EINVAL,
-                "rvq_decode_f32: out must be 16-byte aligned with strides that are multiples of 4");
+                "%s: out must be 16-byte aligned with strides that are multiples of 4", who);
     RVQ_REQUIRE((int64_t)Ktot * C * D < ((int64_t)1 << 30), RVQ_EUNSUPPORTED,
-                "rvq_decode_f32: codebooks of %d x %d x %d elements exceed the 32-bit offsets of the kernel", Ktot, C, D);
+                "%s: codebooks of %d x %d x %d elements exceed the 32-bit offsets of the kernel", who, Ktot, C, D);
     RvqPackView pv = rvq_pack_view(pack, Ktot, C, D);
     if (K == 0) {
         int64_t total = (int64_t)B * D * T;
@@ -218,8 +256,31 @@ extern "C" int rvq_decode_f32(const void *codes, int code_bytes, const int64_t c
         rvq_count_launch(1);
         return rvq_check_launch("rvq_fill_zero_kernel");
     }
-    RVQ_REQUIRE(codes && cs, RVQ_EINVAL, "rvq_decode_f32: null codes");
-    RVQ_REQUIRE(code_bytes == 8 || code_bytes == 4, RVQ_EINVAL, "rvq_decode_f32: codes must be int64 or int32");
-    if (code_bytes == 8) return launch_decode<long long>(codes, cs, B, K, T, pv, out, os, status, stream);
-    return launch_decode<int>(codes, cs, B, K, T, pv, out, os, status, stream);
+    RVQ_REQUIRE(codes && cs, RVQ_EINVAL, "%s: null codes", who);
+    RVQ_REQUIRE(code_bytes == 8 || code_bytes == 4 || code_bytes == 2, RVQ_EINVAL, "%s: codes must be int64, int32 or int16", who);
+    RvqStageOffsets koff;
+    for (int k = 0; k < RVQ_MAX_STAGES; ++k) koff.v[k] = 0;
+    if (steps_late)
+        for (int k = 0; k < K; ++k) {
+            RVQ_REQUIRE(steps_late[k] >= 0, RVQ_EINVAL, "%s: negative delay", who);
+            koff.v[k] = (int64_t)steps_late[k] * cs[2];
+        }
+    if (code_bytes == 8) return launch_decode<long long>(codes, cs, B, K, T, pv, out, os, status, koff, stream);
+    if (code_bytes == 4) return launch_decode<int>(codes, cs, B, K, T, pv, out, os, status, koff, stream);
+    return launch_decode<short>(codes, cs, B, K, T, pv, out, os, status, koff, stream);
+}
+
+extern "C" int rvq_decode_f32(const void *codes, int code_bytes, const int64_t cs[3], int B, int K, int T,
+                              const void *pack, int Ktot, int C, int D, float *out, const int64_t os[3],
+                              int64_t *status, void *stream_) {
+    return decode_common("rvq_decode_f32", codes, code_bytes, cs, B, K, T, pack, Ktot, C, D, out, os, status, nullptr,
+                         (cudaStream_t)stream_);
+}
+
+extern "C" int rvq_decode_delayed_f32(const void *seq, int code_bytes, const int64_t ss[3], int B, int K, int T,
+                                      const int *steps_late, const void *pack, int Ktot, int C, int D, float *out,
+                                      const int64_t os[3], int64_t *status, void *stream_) {
+    RVQ_REQUIRE(steps_late || K == 0, RVQ_EINVAL, "rvq_decode_delayed_f32: null delays");
+    return decode_common("rvq_decode_delayed_f32", seq, code_bytes, ss, B, K, T, pack, Ktot, C, D, out, os, status,
+                         steps_late, (cudaStream_t)stream_);
 }

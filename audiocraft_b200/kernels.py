@@ -97,12 +97,15 @@ def encode(x: torch.Tensor, pack: torch.Tensor, Ktot: int, C: int, K: int, want_
 
 
 def decode(codes: torch.Tensor, pack: torch.Tensor, Ktot: int, C: int, D: int, status: torch.Tensor,
-           out: tp.Optional[torch.Tensor] = None) -> torch.Tensor:
-    """codes [B, K, T] int64/int32 (any strides) -> contiguous [B, T, D] fp32 (the reference's
-    physical layout).  `status` is the int64[2] error word of rvq_decode_f32."""
+           out: tp.Optional[torch.Tensor] = None, steps_late: tp.Optional[tp.Sequence[int]] = None,
+           frames: tp.Optional[int] = None) -> torch.Tensor:
+    """codes [B, K, T] int64 / int32 / int16 (any strides) -> contiguous [B, T, D] fp32 (the reference's
+    physical layout).  `status` is the int64[2] error word of rvq_decode_f32.
+    `steps_late` (with `frames`): `codes` is a delayed-pattern sequence [B, K, S] read in place; stage k's code of
+    frame t is codes[b, k, t + steps_late[k]] and `frames` frames are decoded (rvq_decode_delayed_f32)."""
     lib = _lib.load()
     _require_cuda(codes, "codes")
-    if codes.dtype not in (torch.int64, torch.int32):
+    if codes.dtype not in (torch.int64, torch.int32, torch.int16):
         raise RuntimeError(
             f"Expected tensor for argument #1 'indices' to have one of the following scalar types: Long, Int; "
             f"but got {codes.dtype} instead")
@@ -110,13 +113,23 @@ def decode(codes: torch.Tensor, pack: torch.Tensor, Ktot: int, C: int, D: int, s
         raise ValueError(f"expected codes of shape [B, K, T], got {tuple(codes.shape)}")
     B, K, T = codes.shape
     dev = codes.device
+    if steps_late is not None:
+        if frames is None or len(steps_late) != K or (K and frames + max(steps_late) > T) or frames < 0:
+            raise ValueError("a delayed sequence needs K delays and a frame count with frames + max(delay) <= S")
+        T = int(frames)
     with torch.cuda.device(dev):
         if out is None:
             out = torch.empty((B, T, D), dtype=torch.float32, device=dev)
         if B * T > 0:
-            rc = lib.rvq_decode_f32(codes.data_ptr(), codes.element_size(), _lib.strides3(codes.stride()), B, K, T,
-                                    pack.data_ptr(), Ktot, C, D, out.data_ptr(), _lib.strides3((T * D, 1, D)),
-                                    status.data_ptr(), _stream(dev))
+            if steps_late is None:
+                rc = lib.rvq_decode_f32(codes.data_ptr(), codes.element_size(), _lib.strides3(codes.stride()), B, K, T,
+                                        pack.data_ptr(), Ktot, C, D, out.data_ptr(), _lib.strides3((T * D, 1, D)),
+                                        status.data_ptr(), _stream(dev))
+            else:
+                late = (ctypes.c_int * max(K, 1))(*[int(v) for v in steps_late])
+                rc = lib.rvq_decode_delayed_f32(codes.data_ptr(), codes.element_size(), _lib.strides3(codes.stride()), B, K,
+                                                T, late, pack.data_ptr(), Ktot, C, D, out.data_ptr(),
+                                                _lib.strides3((T * D, 1, D)), status.data_ptr(), _stream(dev))
             _lib.check(rc, "rvq_decode_f32")
     return out
 

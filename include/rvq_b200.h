@@ -145,7 +145,7 @@ int rvq_encode_f32_static(const float *x, const int64_t xs[3], int B, int D, int
 /*
  * ResidualVectorQuantization.decode (core_vq.py:399-405; F.embedding gather core_vq.py:177-179):
  * out = 0.0f + E_0[c_0] + E_1[c_1] + ... in stage order.
- *   codes      device int64 (code_bytes == 8) or int32 (code_bytes == 4); element (b,k,t) at
+ *   codes      device int64 (code_bytes == 8), int32 (4) or int16 (2, the compact cache format); element (b,k,t) at
  *              codes[b*cs[0] + k*cs[1] + t*cs[2]] (strides in elements)
  *   out        device fp32; element (b,d,t) at out[b*os[0] + d*os[1] + t*os[2]].  The reference's
  *              result is physically [B][T][D], i.e. os = {T*D, 1, D}
@@ -157,6 +157,17 @@ int rvq_encode_f32_static(const float *x, const int64_t xs[3], int B, int D, int
 int rvq_decode_f32(const void *codes, int code_bytes, const int64_t cs[3], int B, int K, int T,
                    const void *pack, int Ktot, int C, int D, float *out, const int64_t os[3],
                    int64_t *status, void *stream);
+
+/*
+ * rvq_decode_f32 reading a delayed-pattern sequence in place: Pattern.revert_pattern_sequence
+ * (modules/codebooks_patterns.py:224-246) fused into the gather.  seq is the language model's [B][K][S] token block
+ * (lm.py:531,577); stage k's code of frame t is seq[b][k][t + steps_late[k]], steps_late[k] = offset + delays[k]
+ * (HOST array of K ints; the caller guarantees t + steps_late[k] < S for t < T).  Special tokens (>= C) that a
+ * truncated sequence still holds are reported through `status` like any out-of-range code.
+ */
+int rvq_decode_delayed_f32(const void *seq, int code_bytes, const int64_t ss[3], int B, int K, int T,
+                           const int *steps_late, const void *pack, int Ktot, int C, int D, float *out,
+                           const int64_t os[3], int64_t *status, void *stream);
 
 /*
  * Code-stream plumbing after the tokenizer.  Integer index shuffles, one pass each.

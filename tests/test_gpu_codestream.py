@@ -148,3 +148,40 @@ def test_peer_exchange_wait_times_out_instead_of_hanging():
     kernels.exchange_widen(geo, [b.data_ptr() for b in bufs], 0, 1, out, scratch, status, torch.cuda.current_stream().cuda_stream)
     torch.cuda.synchronize()
     assert status[0].item() == 2 and status[1].item() in (0, 1)
+
+
+def test_decode_reads_delayed_sequences_and_int16_codes_in_place():
+    torch.manual_seed(0)
+    K, T = 4, 333
+    m = ResidualVectorQuantizer(dimension=128, n_q=K, bins=2048, kmeans_init=False).cuda().eval()
+    g = torch.Generator(device="cuda").manual_seed(6)
+    z = torch.randint(0, 2048, (3, K, T), device="cuda", generator=g)
+    pat = cs.DelayedPatternProvider(K).get_pattern(T)
+    seq, _, _ = pat.build_pattern_sequence(z, 2048)
+    with torch.no_grad():
+        want = m.decode(z)
+        got = cs.decode_pattern_sequence(m, seq, pat)
+        got16 = m.decode(cs.to_int16(z))
+    assert torch.equal(got, want) and got.stride() == want.stride()
+    assert torch.equal(got16, want)
+    with pytest.raises(IndexError):   # a truncated sequence still holds special tokens: out of range, as in the reference
+        bad = seq.clone()
+        bad[:, 3, 5] = 2048
+        cs.decode_pattern_sequence(m, bad, pat)
+
+
+def test_small_model_decode_from_shared_memory():
+    """The debug model's codebooks (4 x 400 x 32 fp32 = 205 KB) are staged in shared memory once there are enough
+    frames; the result must not depend on the path."""
+    from tests.golden import gen
+    from tests.test_gpu_parity import make_module, same_bits
+    import oracle
+    embed = gen.codebooks(61, 4, 400, 32)
+    m = make_module(embed, 32, 400)
+    codes = gen.randint(62, (16, 4, 8000), 400)          # 128 000 frames: staged path
+    few = codes[:1, :, :100]                              # 100 frames: rows come from L2
+    with torch.no_grad():
+        big = m.decode(torch.from_numpy(codes).cuda())
+        small = m.decode(torch.from_numpy(few.copy()).cuda())
+    assert same_bits(np.ascontiguousarray(big[:2].cpu().numpy()), np.ascontiguousarray(oracle.decode(codes[:2], embed)))
+    assert torch.equal(small, big[:1, :, :100])

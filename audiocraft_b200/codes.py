@@ -139,6 +139,18 @@ class ParallelPatternProvider(DelayedPatternProvider):
         super().__init__(n_q, [0] * n_q, empty_initial=empty_initial)
 
 
+def decode_compact(quantizer, codes16: torch.Tensor) -> torch.Tensor:
+    """`quantizer.decode` for int16 codes [B, K, T] (the cache format) without widening them first.  (The reference's
+    `decode` rejects int16 indices, so the drop-in method keeps doing that; this is the explicit way in.)"""
+    vq = quantizer.vq
+    Ktot, C, D = vq._shape()
+    status = vq._pack.status(codes16.device)
+    out = kernels.decode(codes16, vq._pack.get(vq._embeds()), Ktot, C, D, status, allow_int16=True)
+    if vq.check_codes:
+        vq.check_errors()
+    return out.transpose(1, 2)
+
+
 def decode_pattern_sequence(quantizer, seq: torch.Tensor, pattern: Pattern) -> torch.Tensor:
     """`quantizer.decode(pattern.revert_pattern_sequence(seq, ...)[0])` in one kernel launch: the gather reads the
     language model's delayed [B, K, S] tokens in place (rvq_decode_delayed_f32).  `seq` must hold every step of the

@@ -98,14 +98,15 @@ def encode(x: torch.Tensor, pack: torch.Tensor, Ktot: int, C: int, K: int, want_
 
 def decode(codes: torch.Tensor, pack: torch.Tensor, Ktot: int, C: int, D: int, status: torch.Tensor,
            out: tp.Optional[torch.Tensor] = None, steps_late: tp.Optional[tp.Sequence[int]] = None,
-           frames: tp.Optional[int] = None) -> torch.Tensor:
-    """codes [B, K, T] int64 / int32 / int16 (any strides) -> contiguous [B, T, D] fp32 (the reference's
-    physical layout).  `status` is the int64[2] error word of rvq_decode_f32.
+           frames: tp.Optional[int] = None, allow_int16: bool = False) -> torch.Tensor:
+    """codes [B, K, T] int64 / int32 (any strides) -> contiguous [B, T, D] fp32 (the reference's physical layout).
+    int16 codes (the compact cache format) are accepted with allow_int16=True; without it they raise like the
+    reference's F.embedding does.  `status` is the int64[2] error word of rvq_decode_f32.
     `steps_late` (with `frames`): `codes` is a delayed-pattern sequence [B, K, S] read in place; stage k's code of
     frame t is codes[b, k, t + steps_late[k]] and `frames` frames are decoded (rvq_decode_delayed_f32)."""
     lib = _lib.load()
     _require_cuda(codes, "codes")
-    if codes.dtype not in (torch.int64, torch.int32, torch.int16):
+    if codes.dtype not in ((torch.int64, torch.int32, torch.int16) if allow_int16 else (torch.int64, torch.int32)):
         raise RuntimeError(
             f"Expected tensor for argument #1 'indices' to have one of the following scalar types: Long, Int; "
             f"but got {codes.dtype} instead")

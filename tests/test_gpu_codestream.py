@@ -161,7 +161,7 @@ def test_decode_reads_delayed_sequences_and_int16_codes_in_place():
     with torch.no_grad():
         want = m.decode(z)
         got = cs.decode_pattern_sequence(m, seq, pat)
-        got16 = m.decode(cs.to_int16(z))
+        got16 = cs.decode_compact(m, cs.to_int16(z))
     assert torch.equal(got, want) and got.stride() == want.stride()
     assert torch.equal(got16, want)
     with pytest.raises(IndexError):   # a truncated sequence still holds special tokens: out of range, as in the reference

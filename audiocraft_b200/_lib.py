@@ -55,6 +55,8 @@ SIGNATURES = {
                                    _i64, _vp]),
     "rvq_decode_f32": (_i32, [_vp, _i32, _i64x3, _i32, _i32, _i32, _vp, _i32, _i32, _i32, _vp, _i64x3, _vp,
                               _vp]),
+    "rvq_ema_update_f32": (_i32, [_vp, _i64x2, _vp, _i32, _i64, _i32, _i32, ctypes.c_float, ctypes.c_float, _vp, _vp, _vp, _vp,
+                                  _vp, _vp]),
     "rvq_decode_delayed_f32": (_i32, [_vp, _i32, _i64x3, _i32, _i32, _i32, ctypes.POINTER(_i32), _vp, _i32, _i32, _i32, _vp,
                                       _i64x3, _vp, _vp]),
 }

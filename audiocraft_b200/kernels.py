@@ -313,3 +313,32 @@ def exchange_widen(geo: ExchangeGeometry, peer_ptrs: tp.Sequence[int], rank: int
     rc = lib.rvq_exchange_widen(ptrs, geo.W, rank, seq % geo.nslots, geo.nslots, seq, geo.slot_bytes, geo.shard_bytes,
                                 geo.K, geo.B, geo.T, geo.axis, out.data_ptr(), scratch.data_ptr(), status.data_ptr(), stream)
     _lib.check(rc, "rvq_exchange_widen")
+
+
+# ---- training-time statistics (include/rvq_b200.h, csrc/rvq_train_stats.cu) ---------------------------------------
+def ema_update(flat: torch.Tensor, codes: torch.Tensor, cluster_size: torch.Tensor, embed_avg: torch.Tensor,
+               embed: torch.Tensor, decay: float, eps: float, want_stats: bool = False):
+    """flat [N, D] fp32 (any strides), codes [N] int64: EMA step of cluster_size / embed_avg and the re-normalised embed,
+    in place (core_vq.py:209-217).  Returns (counts [C], sums [C, D]) when asked."""
+    lib = _lib.load()
+    _require_cuda(flat, "x")
+    for t, name in ((cluster_size, "cluster_size"), (embed_avg, "embed_avg"), (embed, "embed")):
+        if not (t.is_cuda and t.is_contiguous() and t.dtype == torch.float32):
+            raise RuntimeError(f"{name} must be a contiguous fp32 CUDA buffer")
+    if flat.dtype != torch.float32 or flat.dim() != 2 or codes.dtype not in (torch.int64, torch.int32):
+        raise RuntimeError("expected fp32 [N, D] inputs and int64 / int32 codes")
+    N, D = flat.shape
+    C = cluster_size.numel()
+    c = codes.reshape(-1)
+    if not c.is_contiguous():
+        c = c.contiguous()
+    dev = flat.device
+    with torch.cuda.device(dev):
+        counts = torch.empty(C, dtype=torch.float32, device=dev) if want_stats else None
+        sums = torch.empty((C, D), dtype=torch.float32, device=dev) if want_stats else None
+        rc = lib.rvq_ema_update_f32(flat.data_ptr(), _lib._i64x2(int(flat.stride(0)), int(flat.stride(1))), c.data_ptr(),
+                                    c.element_size(), N, C, D, float(decay), float(eps), cluster_size.data_ptr(),
+                                    embed_avg.data_ptr(), embed.data_ptr(), counts.data_ptr() if want_stats else None,
+                                    sums.data_ptr() if want_stats else None, _stream(dev))
+    _lib.check(rc, "rvq_ema_update_f32")
+    return counts, sums

@@ -155,6 +155,14 @@ class EuclideanCodebook(nn.Module):
         """EMA of code usage and of the per-code sum of inputs, then the smoothed re-normalisation
         (core_vq.py:209-217).  The reference forms both statistics through an [N, C] one-hot matrix; here
         they are a histogram and a segmented sum of the same quantities."""
+        if flat.is_cuda:
+            # one pass of librvq_b200.so: ordered per-code sums (no atomics), EMA and re-normalisation fused
+            kernels.ema_update(flat, embed_ind.reshape(-1), self.cluster_size, self.embed_avg, self.embed, self.decay,
+                               self.epsilon)
+            self._pack.invalidate()  # embed was written through a raw pointer: torch's version counter did not move
+            return
+        # host tensors: the same statistics with torch ops (the CPU tests compare this host logic with the reference
+        # step by step; the search itself has no CPU path)
         C = self.codebook_size
         idx = embed_ind.reshape(-1)
         counts = torch.bincount(idx, minlength=C).to(flat.dtype)

@@ -215,6 +215,20 @@ int rvq_delay_revert(const int64_t *seq, const int64_t ss[3], int B, int K, int 
                      uint8_t *mask, void *stream);
 
 /*
+ * Training-time codebook statistics, EuclideanCodebook.forward (core_vq.py:205-217) after the search:
+ *   counts[c] = number of frames with code c (embed_onehot.sum(0), :209); sums[c] = sum of those frames' inputs in
+ *   increasing frame order (x.t() @ embed_onehot, :210); cluster_size and embed_avg take their EMA step
+ *   (ema_inplace, :23-24), embed becomes embed_avg / (laplace_smoothing(cluster_size, C, eps) * cluster_size.sum())
+ *   (:212-217).  No [N, C] one-hot matrix, no atomics: results are deterministic.
+ * x: device fp32, row n at x[n*xs[0] + d*xs[1]] (the flattened channels-last input of the layer); codes: device
+ * int64 / int32 [N]; cluster_size [C], embed_avg [C][D], embed [C][D]: the module's buffers, updated in place;
+ * counts_out [C] / sums_out [C][D]: optional copies of the raw statistics (NULL to skip).  D <= 1024.
+ */
+int rvq_ema_update_f32(const float *x, const int64_t xs[2], const void *codes, int code_bytes, int64_t N, int C, int D,
+                       float decay, float eps, float *cluster_size, float *embed_avg, float *embed,
+                       float *counts_out, float *sums_out, void *stream);
+
+/*
  * Diagnostics (no counterpart in the reference): runs the tensor-core encode and also returns, for
  * the first 128 frames and stage `stage`, the raw approximate scores of every code
  * (acc_out, device fp32 [128][C]) and the per-frame scan state (info_out, device buffer of

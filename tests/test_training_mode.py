@@ -177,5 +177,5 @@ def test_ema_statistics_kernel_is_deterministic_and_ordered():
     ea_ref = bufs0[1] * decay + sums * (1 - decay)
     tot = cs_ref.sum()
     em_ref = ea_ref / (((cs_ref + eps) / (tot + C * eps)) * tot).unsqueeze(1)
-    assert torch.allclose(cs_, cs_ref, rtol=1e-6) and torch.allclose(ea, ea_ref, rtol=1e-6, atol=1e-7)
+    assert torch.allclose(cs_, cs_ref, rtol=1e-5) and torch.allclose(ea, ea_ref, rtol=1e-5, atol=1e-6)
     assert torch.allclose(em, em_ref, rtol=1e-5, atol=1e-6)

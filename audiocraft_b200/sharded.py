@@ -280,3 +280,30 @@ class ShardedRVQ:
     def decode(self, codes_global: torch.Tensor) -> torch.Tensor:
         """Decodes this rank's slice of gathered codes (local result; latents are not gathered)."""
         return self.decode_local(self.local_slice(codes_global))
+
+
+def average_buffers(module, group: tp.Optional[dist.ProcessGroup] = None) -> None:
+    """Data-parallel training: the quantizer's buffers (`inited`, `cluster_size`, `embed`, `embed_avg` of every
+    layer) become their mean over the workers, as `flashy.distrib.average_tensors(self.rvq.buffers())` does after a
+    training step of the style conditioner (modules/conditioners.py:963).  One all-reduce over one flat fp32 buffer
+    per call instead of one collective per tensor (4 per layer); the derived codebook pack is invalidated."""
+    if not (dist.is_available() and dist.is_initialized()):
+        return
+    world = dist.get_world_size(group)
+    if world == 1:
+        return
+    bufs = [b for b in module.buffers() if b.is_floating_point()]
+    if not bufs:
+        return
+    flat = torch.cat([b.detach().reshape(-1).to(torch.float32) for b in bufs])
+    dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
+    flat.div_(world)
+    off = 0
+    with torch.no_grad():
+        for b in bufs:
+            n = b.numel()
+            b.copy_(flat[off:off + n].view_as(b))
+            off += n
+    vq = getattr(module, "vq", None)
+    if vq is not None and hasattr(vq, "invalidate_cache"):
+        vq.invalidate_cache()

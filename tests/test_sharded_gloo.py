@@ -101,3 +101,33 @@ def test_world2_gloo_encode_gather_matches_single_process(shape, wire_int16):
     axis = shard_axis(B, T, world)
     got = np.concatenate([out[r][1] for r in range(world)], axis=0 if axis == 0 else 2)
     assert np.array_equal(got, full)
+
+
+def _avg_worker(rank, world, port, out):
+    from audiocraft_b200.quantization import ResidualVectorQuantizer
+    from audiocraft_b200.sharded import average_buffers
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        torch.manual_seed(10 + rank)
+        m = ResidualVectorQuantizer(dimension=16, n_q=2, bins=8, kmeans_init=False)
+        for b in m.buffers():
+            b.add_(float(rank))
+        before = {k: v.clone() for k, v in m.state_dict().items()}
+        average_buffers(m)
+        out[rank] = (before, {k: v.clone() for k, v in m.state_dict().items()})
+    finally:
+        dist.destroy_process_group()
+
+
+def test_world2_gloo_average_buffers_is_the_mean_over_workers():
+    """flashy.distrib.average_tensors(rvq.buffers()) (modules/conditioners.py:963) as one flat all-reduce."""
+    mgr = mp.Manager()
+    out = mgr.dict()
+    mp.spawn(_avg_worker, args=(2, _free_port(), out), nprocs=2, join=True)
+    b0, a0 = out[0]
+    b1, a1 = out[1]
+    for k in b0:
+        want = (b0[k] + b1[k]) / 2
+        assert torch.allclose(a0[k], want) and torch.equal(a0[k], a1[k]), k

@@ -38,9 +38,10 @@ SIGNATURES = {
                                    _i32, _vp]),
     "rvq_widen_codes_i16": (_i32, [_vp, _i32, _i32, _i32, _i32, _i32, _vp, _vp]),
     "rvq_exchange_header_bytes": (_i64, []),
-    "rvq_exchange_push": (_i32, [ctypes.POINTER(_vp), _i32, _i32, _i32, _i32, ctypes.c_uint32, _i64, _i64, _vp, _vp, _vp]),
+    "rvq_exchange_push": (_i32, [ctypes.POINTER(_vp), _i32, _i32, _i32, _i32, ctypes.c_uint32, _i64, _i64, _vp, _vp, _i32,
+                                 _vp]),
     "rvq_exchange_widen": (_i32, [ctypes.POINTER(_vp), _i32, _i32, _i32, _i32, ctypes.c_uint32, _i64, _i64, _i32, _i32, _i32,
-                                  _i32, _vp, _vp, _vp, _vp]),
+                                  _i32, _vp, _vp, _vp, _i32, _vp]),
     "rvq_codes_convert": (_i32, [_vp, _i32, _i64x3, _i32, _i32, _i32, _vp, _i32, _i64x3, _vp]),
     "rvq_codes_packed_bytes": (_i64, [_i64, _i32]),
     "rvq_codes_pack_bits": (_i32, [_vp, _i64, _i32, _vp, _vp]),

@@ -13,8 +13,12 @@
 //   push(seq):  wait until every peer has acknowledged step seq - nslots (it has widened the slot's previous
 //               contents), copy my shard into every rank's slot (mine included), then data[slot][me] = seq everywhere
 //   widen(seq): wait until data[slot][r] >= seq for every r, widen, then ack[slot][me] = seq everywhere
-// Every wait gives up after about 50 ms, records that in the status word (the host raises) and carries on: a lost
-// peer must not hang the GPU.
+// The waits are stream memory operations (cuStreamBatchMemOp, WAIT_VALUE_32 with GEQ): the stream itself holds the
+// kernels back until the flags are there, so no CTA sits on an SM spinning while it waits for another GPU -- the
+// persistent encode kernel of the next step needs every SM whole.  (spin_wait = 1 selects an in-kernel wait instead,
+// which gives up after about 50 ms, records that in the status word and carries on.)
+#include <cuda.h>
+
 #include "rvq_common.cuh"
 
 namespace {
@@ -85,9 +89,9 @@ __device__ __forceinline__ bool last_block(unsigned int *ticket) {
 
 __global__ void __launch_bounds__(TPB) push_kernel(Peers peers, int W, int rank, int slot, int nslots, uint32_t seq,
                                                    int64_t slot_bytes, int64_t shard_bytes, unsigned int *ticket,
-                                                   int64_t *status) {
+                                                   int64_t *status, int spin) {
     unsigned char *mine = peers.base[rank];
-    wait_flags(true, mine, W, slot, seq > (uint32_t)nslots ? seq - (uint32_t)nslots : 0u, status, 1);
+    if (spin) wait_flags(true, mine, W, slot, seq > (uint32_t)nslots ? seq - (uint32_t)nslots : 0u, status, 1);
     const int64_t off = FLAG_BYTES + (int64_t)slot * slot_bytes + (int64_t)rank * shard_bytes;
     const uint4 *src = reinterpret_cast<const uint4 *>(mine + off);
     const int64_t n16 = shard_bytes / 16;
@@ -108,9 +112,9 @@ __device__ __forceinline__ void shard_of(int c, int base, int extra, int &r, int
 
 __global__ void __launch_bounds__(TPB) widen_wait_kernel(Peers peers, int W, int rank, int slot, uint32_t seq, int64_t slot_bytes,
                                                          int64_t shard_bytes, int K, int B, int T, int axis,
-                                                         int64_t *__restrict__ out, unsigned int *ticket, int64_t *status) {
+                                                         int64_t *__restrict__ out, unsigned int *ticket, int64_t *status, int spin) {
     unsigned char *mine = peers.base[rank];
-    wait_flags(false, mine, W, slot, seq, status, 2);
+    if (spin) wait_flags(false, mine, W, slot, seq, status, 2);
     const unsigned char *slot_base = mine + FLAG_BYTES + (int64_t)slot * slot_bytes;
     const int n = axis == 0 ? B : T, base = n / W, extra = n % W, smax = base + (extra ? 1 : 0);
     const int64_t total = (int64_t)K * B * T;
@@ -137,12 +141,38 @@ int fill_peers(const char *who, void *const *peer_base, int W, int rank, Peers &
     return RVQ_OK;
 }
 
+// stream-ordered wait until flag[p] >= want for every p != rank (cyclic comparison); flags live in MY buffer
+int stream_wait_flags(const char *who, unsigned char *mine, bool acks, int W, int rank, int slot, uint32_t want, cudaStream_t stream) {
+    if (want == 0 || W == 1) return RVQ_OK;
+    CUstreamBatchMemOpParams ops[MAXW];
+    int n = 0;
+    for (int p = 0; p < W; ++p) {
+        if (p == rank) continue;
+        const uintptr_t addr = (uintptr_t)mine + (acks ? 2048 : 0) + 64u * (uintptr_t)(slot * W + p);
+        ops[n] = CUstreamBatchMemOpParams();
+        ops[n].operation = CU_STREAM_MEM_OP_WAIT_VALUE_32;
+        ops[n].waitValue.address = (CUdeviceptr)addr;
+        ops[n].waitValue.value = want;
+        ops[n].waitValue.flags = CU_STREAM_WAIT_VALUE_GEQ;
+        ++n;
+    }
+    CUresult r = cuStreamBatchMemOp((CUstream)stream, (unsigned)n, ops, 0);
+    if (r != CUDA_SUCCESS) {
+        const char *msg = nullptr;
+        cuGetErrorString(r, &msg);
+        rvq_set_error("%s: cuStreamBatchMemOp failed: %s", who, msg ? msg : "?");
+        return RVQ_ECUDA;
+    }
+    return RVQ_OK;
+}
+
 }  // namespace
 
 extern "C" int64_t rvq_exchange_header_bytes(void) { return FLAG_BYTES; }
 
 extern "C" int rvq_exchange_push(void *const *peer_base, int W, int rank, int slot, int nslots, uint32_t seq,
-                                 int64_t slot_bytes, int64_t shard_bytes, void *scratch, int64_t *status, void *stream) {
+                                 int64_t slot_bytes, int64_t shard_bytes, void *scratch, int64_t *status, int spin_wait,
+                                 void *stream) {
     Peers p;
     int rc = fill_peers("rvq_exchange_push", peer_base, W, rank, p);
     if (rc != RVQ_OK) return rc;
@@ -153,15 +183,21 @@ extern "C" int rvq_exchange_push(void *const *peer_base, int W, int rank, int sl
     int64_t blocks = (n16 + TPB * 4 - 1) / (TPB * 4);
     if (blocks > 32) blocks = 32;  // a few SMs' worth: NVLink, not the SMs, carries this
     if (blocks < 1) blocks = 1;
+    const int spin = spin_wait ? 1 : 0;
+    if (!spin) {
+        rc = stream_wait_flags("rvq_exchange_push", p.base[rank], true, W, rank, slot,
+                               seq > (uint32_t)nslots ? seq - (uint32_t)nslots : 0u, (cudaStream_t)stream);
+        if (rc != RVQ_OK) return rc;
+    }
     push_kernel<<<(unsigned)blocks, TPB, 0, (cudaStream_t)stream>>>(p, W, rank, slot, nslots, seq, slot_bytes, shard_bytes,
-                                                                   (unsigned int *)scratch, status);
+                                                                   (unsigned int *)scratch, status, spin);
     rvq_count_launch(1);
     return rvq_check_launch("rvq_exchange_push");
 }
 
 extern "C" int rvq_exchange_widen(void *const *peer_base, int W, int rank, int slot, int nslots, uint32_t seq,
                                   int64_t slot_bytes, int64_t shard_bytes, int K, int B, int T, int axis, int64_t *codes,
-                                  void *scratch, int64_t *status, void *stream) {
+                                  void *scratch, int64_t *status, int spin_wait, void *stream) {
     Peers p;
     int rc = fill_peers("rvq_exchange_widen", peer_base, W, rank, p);
     if (rc != RVQ_OK) return rc;
@@ -172,8 +208,13 @@ extern "C" int rvq_exchange_widen(void *const *peer_base, int W, int rank, int s
     int64_t blocks = (total + TPB * 8 - 1) / (TPB * 8);
     if (blocks > 148 * 4) blocks = 148 * 4;
     if (blocks < 1) blocks = 1;
+    const int spin = spin_wait ? 1 : 0;
+    if (!spin) {
+        rc = stream_wait_flags("rvq_exchange_widen", p.base[rank], false, W, rank, slot, seq, (cudaStream_t)stream);
+        if (rc != RVQ_OK) return rc;
+    }
     widen_wait_kernel<<<(unsigned)blocks, TPB, 0, (cudaStream_t)stream>>>(p, W, rank, slot, seq, slot_bytes, shard_bytes, K, B, T,
-                                                                         axis, codes, (unsigned int *)scratch + 16, status);
+                                                                         axis, codes, (unsigned int *)scratch + 16, status, spin);
     rvq_count_launch(1);
     return rvq_check_launch("rvq_exchange_widen");
 }

@@ -298,20 +298,21 @@ class ExchangeGeometry:
 
 
 def exchange_push(geo: ExchangeGeometry, peer_ptrs: tp.Sequence[int], rank: int, seq: int, scratch: torch.Tensor,
-                  status: torch.Tensor, stream: int) -> None:
+                  status: torch.Tensor, stream: int, spin_wait: bool = False) -> None:
     lib = _lib.load()
     ptrs = (ctypes.c_void_p * geo.W)(*[int(p) for p in peer_ptrs])
     rc = lib.rvq_exchange_push(ptrs, geo.W, rank, seq % geo.nslots, geo.nslots, seq, geo.slot_bytes, geo.shard_bytes,
-                               scratch.data_ptr(), status.data_ptr(), stream)
+                               scratch.data_ptr(), status.data_ptr(), 1 if spin_wait else 0, stream)
     _lib.check(rc, "rvq_exchange_push")
 
 
 def exchange_widen(geo: ExchangeGeometry, peer_ptrs: tp.Sequence[int], rank: int, seq: int, out: torch.Tensor,
-                   scratch: torch.Tensor, status: torch.Tensor, stream: int) -> None:
+                   scratch: torch.Tensor, status: torch.Tensor, stream: int, spin_wait: bool = False) -> None:
     lib = _lib.load()
     ptrs = (ctypes.c_void_p * geo.W)(*[int(p) for p in peer_ptrs])
     rc = lib.rvq_exchange_widen(ptrs, geo.W, rank, seq % geo.nslots, geo.nslots, seq, geo.slot_bytes, geo.shard_bytes,
-                                geo.K, geo.B, geo.T, geo.axis, out.data_ptr(), scratch.data_ptr(), status.data_ptr(), stream)
+                                geo.K, geo.B, geo.T, geo.axis, out.data_ptr(), scratch.data_ptr(), status.data_ptr(),
+                                1 if spin_wait else 0, stream)
     _lib.check(rc, "rvq_exchange_widen")
 
 

@@ -215,8 +215,19 @@ class ShardedRVQ:
             if out is None:
                 out = torch.empty((K, B, T), dtype=torch.int64, device=dev)
             stream = torch.cuda.current_stream(dev).cuda_stream
-            kernels.exchange_push(st["geo"], st["ptrs"], self.rank, bufs["seq"], st["scratch"], st["status"], stream)
-            kernels.exchange_widen(st["geo"], st["ptrs"], self.rank, bufs["seq"], out, st["scratch"], st["status"], stream)
+            spin = st.get("spin", False)
+            try:
+                kernels.exchange_push(st["geo"], st["ptrs"], self.rank, bufs["seq"], st["scratch"], st["status"], stream,
+                                      spin_wait=spin)
+            except RuntimeError:
+                if spin:
+                    raise
+                # stream memory operations refused (driver / memory type): wait inside the kernels instead
+                spin = st["spin"] = True
+                kernels.exchange_push(st["geo"], st["ptrs"], self.rank, bufs["seq"], st["scratch"], st["status"], stream,
+                                      spin_wait=True)
+            kernels.exchange_widen(st["geo"], st["ptrs"], self.rank, bufs["seq"], out, st["scratch"], st["status"], stream,
+                                   spin_wait=spin)
             ev = torch.cuda.Event()
             ev.record(torch.cuda.current_stream(dev))
             st["free"][bufs["seq"] % st["geo"].nslots] = ev

@@ -369,11 +369,21 @@ def run_gpu_arm(args, rank: int, world: int, local_rank: int):
             return gathered
         return None
 
-    def sync_all():
+    def sync_all(settle: bool = False):
         torch.cuda.synchronize(dev)
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize(dev)
+        if settle and world > 1:
+            # The ranks leave the barrier a millisecond or two apart (host wake-up), and the code exchange couples
+            # them with two steps of slack: the rank that starts first then waits for the last one inside the timed
+            # region.  Agree on a wall-clock start (one host, one clock) and spin up to it.
+            t0 = torch.tensor([time.time() + 0.02], dtype=torch.float64, device=dev)
+            dist.all_reduce(t0, op=dist.ReduceOp.MAX)
+            t_start = float(t0.item())
+            torch.cuda.synchronize(dev)
+            while time.time() < t_start:
+                pass
 
     # ---- device-resident timing -------------------------------------------------------------
     with torch.no_grad():
@@ -406,7 +416,10 @@ def run_gpu_arm(args, rank: int, world: int, local_rank: int):
             for e in e3:
                 e.record()
         start.record(); end.record()
-        sync_all()
+        sync_all(settle=True)
+        if os.environ.get("BENCH_PING") and world > 1:
+            step(0)
+            torch.cuda.synchronize(dev)
         import gc
         gc.collect()
         gc.disable()

@@ -103,15 +103,18 @@ int rvq_widen_codes_i16(const int16_t *recv, int W, int K, int B, int T, int axi
  *   rvq_exchange_push   stores this rank's shard into every peer's slot over NVLink and raises this rank's data flag
  *                       there (after waiting, for seq > nslots, until every peer has consumed step seq - nslots)
  *   rvq_exchange_widen  waits for the data flags of all ranks, writes codes int64 [K][B][T], acknowledges the slot
- * scratch: 256 zeroed device bytes private to the caller; status: device int64[2], zeroed; a wait that lasts longer
- * than 50 ms writes status[0] = 1 (push) / 2 (widen) and status[1] = the rank waited for, and the kernel carries on.
+ * Waiting: spin_wait == 0 (normal): the waits are stream memory operations (cuStreamBatchMemOp, WAIT_VALUE_32), no
+ * CTA occupies an SM while another GPU is late; spin_wait == 1: the kernels wait themselves and give up after about
+ * 50 ms, writing status[0] = 1 (push) / 2 (widen) and status[1] = the rank waited for, and carry on.
+ * scratch: 256 zeroed device bytes private to the caller; status: device int64[2], zeroed.
  */
 int64_t rvq_exchange_header_bytes(void);
 int rvq_exchange_push(void *const *peer_base, int W, int rank, int slot, int nslots, uint32_t seq,
-                      int64_t slot_bytes, int64_t shard_bytes, void *scratch, int64_t *status, void *stream);
+                      int64_t slot_bytes, int64_t shard_bytes, void *scratch, int64_t *status, int spin_wait,
+                      void *stream);
 int rvq_exchange_widen(void *const *peer_base, int W, int rank, int slot, int nslots, uint32_t seq,
                        int64_t slot_bytes, int64_t shard_bytes, int K, int B, int T, int axis, int64_t *codes,
-                       void *scratch, int64_t *status, void *stream);
+                       void *scratch, int64_t *status, int spin_wait, void *stream);
 
 /*
  * rvq_encode_f32 for callers that may not allocate.  No counterpart in the reference.

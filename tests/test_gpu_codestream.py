@@ -103,8 +103,9 @@ def test_delay_pattern_build_and_revert(K, T, delays, empty_initial):
     assert np.array_equal(back.cpu().numpy(), rv) and np.array_equal(bm.cpu().numpy(), rm)
 
 
+@pytest.mark.parametrize("spin", [False, True])
 @pytest.mark.parametrize("B,T,W", [(7, 300, 2), (16, 700, 8), (2, 1000, 3)])
-def test_peer_exchange_emulated_ranks(B, T, W):
+def test_peer_exchange_emulated_ranks(B, T, W, spin):
     """The NVLink exchange (rvq_exchange_push / rvq_exchange_widen) with W ranks emulated on one GPU: W plain device
     buffers stand in for the peers' symmetric buffers, the ranks' kernels run one after the other on one stream (every
     flag a kernel waits for is already set when it starts).  Five steps, two slots: slots and flags are reused."""
@@ -129,10 +130,10 @@ def test_peer_exchange_emulated_ranks(B, T, W):
                 wire = shard[:, :hi - lo] if geo.axis == 0 else shard[:, :, :hi - lo]
                 m.vq.encode(xr, n_q=K, wire=wire)
             for r in range(W):
-                kernels.exchange_push(geo, ptrs, r, seq, scratch[r], status[r], st)
+                kernels.exchange_push(geo, ptrs, r, seq, scratch[r], status[r], st, spin_wait=spin)
             for r in range(W):
                 out = torch.empty((K, B, T), dtype=torch.int64, device="cuda")
-                kernels.exchange_widen(geo, ptrs, r, seq, out, scratch[r], status[r], st)
+                kernels.exchange_widen(geo, ptrs, r, seq, out, scratch[r], status[r], st, spin_wait=spin)
                 assert torch.equal(out.transpose(0, 1), whole), f"step {seq}, rank {r}"
     for r in range(W):
         assert status[r].tolist() == [0, 0]
@@ -145,7 +146,8 @@ def test_peer_exchange_wait_times_out_instead_of_hanging():
     scratch = torch.zeros(256, dtype=torch.uint8, device="cuda")
     status = torch.zeros(2, dtype=torch.int64, device="cuda")
     out = torch.empty((4, 4, 64), dtype=torch.int64, device="cuda")
-    kernels.exchange_widen(geo, [b.data_ptr() for b in bufs], 0, 1, out, scratch, status, torch.cuda.current_stream().cuda_stream)
+    kernels.exchange_widen(geo, [b.data_ptr() for b in bufs], 0, 1, out, scratch, status, torch.cuda.current_stream().cuda_stream,
+                           spin_wait=True)   # (the stream-operation wait would wait for ever: that is its contract)
     torch.cuda.synchronize()
     assert status[0].item() == 2 and status[1].item() in (0, 1)
 

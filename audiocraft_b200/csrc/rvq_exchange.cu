@@ -156,13 +156,20 @@ int stream_wait_flags(const char *who, unsigned char *mine, bool acks, int W, in
         ops[n].waitValue.flags = CU_STREAM_WAIT_VALUE_GEQ;
         ++n;
     }
-    CUresult r = cuStreamBatchMemOp((CUstream)stream, (unsigned)n, ops, 0);
-    if (r != CUDA_SUCCESS) {
-        const char *msg = nullptr;
-        cuGetErrorString(r, &msg);
-        rvq_set_error("%s: cuStreamBatchMemOp failed: %s", who, msg ? msg : "?");
-        return RVQ_ECUDA;
-    }
+    // the driver entry point is looked up through the runtime, so that the library itself does not depend on libcuda
+    // (it must load, for its host-only entry points, on machines without a driver)
+    typedef CUresult (*BatchMemOpFn)(CUstream, unsigned int, CUstreamBatchMemOpParams *, unsigned int);
+    static BatchMemOpFn fn = [] {
+        void *p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuStreamBatchMemOp", &p, cudaEnableDefault, &q) != cudaSuccess ||
+            q != cudaDriverEntryPointSuccess)
+            p = nullptr;
+        return (BatchMemOpFn)p;
+    }();
+    RVQ_REQUIRE(fn != nullptr, RVQ_ECUDA, "%s: the driver does not offer cuStreamBatchMemOp", who);
+    CUresult r = fn((CUstream)stream, (unsigned)n, ops, 0);
+    RVQ_REQUIRE(r == CUDA_SUCCESS, RVQ_ECUDA, "%s: cuStreamBatchMemOp failed with CUresult %d", who, (int)r);
     return RVQ_OK;
 }
 

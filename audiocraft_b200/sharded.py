@@ -250,7 +250,9 @@ class ShardedRVQ:
             return codes_local, ev
         dev = codes_local.device
         if getattr(self, "_gather_stream", None) is None:
-            self._gather_stream = torch.cuda.Stream(dev)
+            # high priority: when SMs free up between two persistent encode kernels, the exchange's few small blocks
+            # go first instead of waiting a whole encode for room
+            self._gather_stream = torch.cuda.Stream(dev, priority=-1)
         gs = self._gather_stream
         cur = torch.cuda.current_stream(dev)
         B, K, T = global_shape

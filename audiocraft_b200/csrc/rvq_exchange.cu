@@ -6,9 +6,9 @@
 // SURVEY.md 2a; design in SURVEY.md 5 "stretch" and 7.4.)
 //
 // Symmetric buffer of a rank (same layout on every rank, allocated and exchanged by sharded.py):
-//   [0, 4096)                       flags, uint32: data[slot][src rank] at 16 * (slot * W + src),
-//                                   ack[slot][consumer rank] at 2048 / 4 + 16 * (slot * W + consumer)   (64-byte apart)
-//   4096 + slot * slot_bytes + r * shard_bytes   rank r's codes of the step that uses `slot`
+//   [0, 16384)                      flags, uint32, 64 bytes apart: data[slot][src rank] at byte 64 * (slot * W + src),
+//                                   ack[slot][consumer rank] at byte 8192 + 64 * (slot * W + consumer)
+//   16384 + slot * slot_bytes + r * shard_bytes   rank r's codes of the step that uses `slot`
 // A step is numbered seq = 1, 2, ... and uses slot seq % nslots.  Flags only grow.
 //   push(seq):  wait until every peer has acknowledged step seq - nslots (it has widened the slot's previous
 //               contents), copy my shard into every rank's slot (mine included), then data[slot][me] = seq everywhere
@@ -25,7 +25,8 @@ namespace {
 
 constexpr int MAXW = 16;
 constexpr int TPB = 256;
-constexpr int64_t FLAG_BYTES = 4096;
+constexpr int64_t FLAG_BYTES = 16384;  // data flags in the first half, acknowledgements in the second
+constexpr int64_t ACK_OFFSET = FLAG_BYTES / 2;
 constexpr long long TIMEOUT_NS = 50LL * 1000 * 1000;
 
 struct Peers {
@@ -49,7 +50,7 @@ __device__ __forceinline__ uint32_t *data_flag(unsigned char *base, int W, int s
     return reinterpret_cast<uint32_t *>(base) + 16 * (slot * W + src);
 }
 __device__ __forceinline__ uint32_t *ack_flag(unsigned char *base, int W, int slot, int consumer) {
-    return reinterpret_cast<uint32_t *>(base + 2048) + 16 * (slot * W + consumer);
+    return reinterpret_cast<uint32_t *>(base + ACK_OFFSET) + 16 * (slot * W + consumer);
 }
 // thread p < W of the block waits for flag p; everybody leaves together.  Returns false after a timeout.
 __device__ bool wait_flags(bool acks, unsigned char *mine, int W, int slot, uint32_t want, int64_t *status, int what) {
@@ -148,7 +149,7 @@ int stream_wait_flags(const char *who, unsigned char *mine, bool acks, int W, in
     int n = 0;
     for (int p = 0; p < W; ++p) {
         if (p == rank) continue;
-        const uintptr_t addr = (uintptr_t)mine + (acks ? 2048 : 0) + 64u * (uintptr_t)(slot * W + p);
+        const uintptr_t addr = (uintptr_t)mine + (acks ? ACK_OFFSET : 0) + 64u * (uintptr_t)(slot * W + p);
         ops[n] = CUstreamBatchMemOpParams();
         ops[n].operation = CU_STREAM_MEM_OP_WAIT_VALUE_32;
         ops[n].waitValue.address = (CUdeviceptr)addr;
@@ -183,7 +184,7 @@ extern "C" int rvq_exchange_push(void *const *peer_base, int W, int rank, int sl
     Peers p;
     int rc = fill_peers("rvq_exchange_push", peer_base, W, rank, p);
     if (rc != RVQ_OK) return rc;
-    RVQ_REQUIRE(nslots >= 1 && slot >= 0 && slot < nslots && nslots * W * 64 <= 2048 && seq >= 1 && shard_bytes > 0 &&
+    RVQ_REQUIRE(nslots >= 1 && slot >= 0 && slot < nslots && (int64_t)nslots * W * 64 <= ACK_OFFSET && seq >= 1 && shard_bytes > 0 &&
                     shard_bytes % 16 == 0 && slot_bytes >= (int64_t)W * shard_bytes && slot_bytes % 16 == 0 && scratch && status,
                 RVQ_EINVAL, "rvq_exchange_push: bad slot geometry");
     const int64_t n16 = shard_bytes / 16;

@@ -134,13 +134,17 @@ class ShardedRVQ:
         state = None
         try:
             import torch.distributed._symmetric_memory as symm_mem
-            geo = kernels.ExchangeGeometry(self.world, K, B, T, nslots=2)
+            # slots = how many steps the exchange may lag behind the encodes before an encode has to wait for it: as many
+            # as fit 256 MB (and the flag area), at least two
+            probe = kernels.ExchangeGeometry(self.world, K, B, T, nslots=2)
+            nslots = int(max(2, min(8, 128 // self.world, (256 << 20) // max(probe.slot_bytes, 1))))
+            geo = kernels.ExchangeGeometry(self.world, K, B, T, nslots=nslots)
             buf = symm_mem.empty(geo.total_bytes, dtype=torch.uint8, device=device)
             hdl = symm_mem.rendezvous(buf, self.group if self.group is not None else dist.group.WORLD)
             buf.zero_()
             torch.cuda.synchronize(device)
             dist.barrier(group=self.group)     # nobody pushes into a buffer that is still being cleared
-            state = {"geo": geo, "buf": buf, "hdl": hdl, "ptrs": [int(p) for p in hdl.buffer_ptrs], "seq": 0, "free": [None, None],
+            state = {"geo": geo, "buf": buf, "hdl": hdl, "ptrs": [int(p) for p in hdl.buffer_ptrs], "seq": 0, "free": [None] * nslots,
                      "scratch": torch.zeros(256, dtype=torch.uint8, device=device),
                      "status": torch.zeros(2, dtype=torch.int64, device=device)}
         except Exception as e:  # symmetric memory not available for this group / driver

@@ -76,7 +76,35 @@ def measured_peaks():
 # ------------------------------------------------------------------------------------------------
 # clock sampling during the timed region (NVML; nvidia-smi as a fallback)
 # ------------------------------------------------------------------------------------------------
+_SAMPLER_SRC = r"""
+import sys, time
+import pynvml as nv
+nv.nvmlInit()
+bus = sys.argv[1]
+h = None
+for i in range(nv.nvmlDeviceGetCount()):
+    hh = nv.nvmlDeviceGetHandleByIndex(i)
+    b = nv.nvmlDeviceGetPciInfo(hh).busId
+    b = b.decode() if isinstance(b, bytes) else b
+    if bus and b.lower().endswith(bus.lower()):
+        h = hh
+if h is None:
+    h = nv.nvmlDeviceGetHandleByIndex(int(sys.argv[2]))
+print("max", nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM), flush=True)
+while True:
+    try:
+        print(repr(time.time()), nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM),
+              nv.nvmlDeviceGetCurrentClocksThrottleReasons(h), flush=True)
+    except Exception:
+        pass
+    time.sleep(0.002)
+"""
+
+
 class ClockSampler:
+    """SM clock and throttle reasons every 2 ms, from a SEPARATE process (NVML queries made from the benchmark's own
+    process now and then hold up its kernel launches for a millisecond or two, which a 7 ms timed region cannot hide).
+    The samples carry wall-clock times; those inside [t_begin, t_end] are the ones reported."""
     REASONS = {
         0x1: "gpu_idle", 0x2: "applications_clocks_setting", 0x4: "sw_power_cap", 0x8: "hw_slowdown",
         0x10: "sync_boost", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown",
@@ -84,61 +112,58 @@ class ClockSampler:
     }
 
     def __init__(self, index: int):
-        self.index = index
-        self.samples, self.reasons = [], set()
-        self.active = False
-        self.sm_max = None
-        self._stop = threading.Event()
-        self._thr = None
-        self._nvml = None
+        import subprocess
+        self.proc = None
+        self.t_begin = self.t_end = None
         try:
-            import pynvml
-            pynvml.nvmlInit()
-            self._nvml = pynvml
-            # honour CUDA_VISIBLE_DEVICES: map through the PCI bus id of the torch device
             import torch
-            bus = torch.cuda.get_device_properties(index).pci_bus_id if hasattr(
-                torch.cuda.get_device_properties(index), "pci_bus_id") else None
-            self._h = None
-            if bus is not None:
-                for i in range(pynvml.nvmlDeviceGetCount()):
-                    h = pynvml.nvmlDeviceGetHandleByIndex(i)
-                    if pynvml.nvmlDeviceGetPciInfo(h).bus == bus:
-                        self._h = h
-            if self._h is None:
-                self._h = pynvml.nvmlDeviceGetHandleByIndex(index)
-            self.sm_max = int(pynvml.nvmlDeviceGetMaxClockInfo(self._h, pynvml.NVML_CLOCK_SM))
+            props = torch.cuda.get_device_properties(index)
+            bus = ""
+            if hasattr(props, "pci_bus_id"):
+                bus = "%02x:%02x.0" % (props.pci_bus_id, getattr(props, "pci_device_id", 0))
+            self.proc = subprocess.Popen([sys.executable, "-c", _SAMPLER_SRC, bus, str(index)], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
         except Exception as e:  # pragma: no cover
-            log(f"[bench] NVML unavailable ({e}); clocks not sampled")
-            self._nvml = None
+            log(f"[bench] clock sampler unavailable ({e})")
 
-    def _run(self):
-        nv = self._nvml
-        while not self._stop.is_set():
-            try:
-                clk = int(nv.nvmlDeviceGetClockInfo(self._h, nv.NVML_CLOCK_SM))
-                mask = int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(self._h))
-                if self.active:  # only the timed region counts
-                    self.samples.append(clk)
-                    for bit, name in self.REASONS.items():
-                        if mask & bit and name != "gpu_idle":
-                            self.reasons.add(name)
-            except Exception:  # pragma: no cover
-                pass
-            time.sleep(0.002)
+    @property
+    def active(self):
+        return self.t_begin is not None and self.t_end is None
+
+    @active.setter
+    def active(self, on: bool):
+        if on:
+            self.t_begin, self.t_end = time.time(), None
+        else:
+            self.t_end = time.time()
 
     def start(self):
-        if self._nvml is not None:
-            self._thr = threading.Thread(target=self._run, daemon=True)
-            self._thr.start()
+        pass
 
     def stop(self):
-        if self._thr is not None:
-            self._stop.set()
-            self._thr.join()
-        s = sorted(self.samples)
-        med = s[len(s) // 2] if s else None
-        return {"sm_mhz": med, "sm_max_mhz": self.sm_max, "reasons": sorted(self.reasons), "samples": len(s)}
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        self.proc.terminate()
+        try:
+            out, _ = self.proc.communicate(timeout=5)
+        except Exception:  # pragma: no cover
+            self.proc.kill()
+            out = ""
+        sm_max, clocks, reasons = None, [], set()
+        for line in out.splitlines():
+            parts = line.split()
+            if len(parts) == 2 and parts[0] == "max":
+                sm_max = int(parts[1])
+            elif len(parts) == 3:
+                t, clk, mask = float(parts[0]), int(parts[1]), int(parts[2])
+                if self.t_begin is not None and self.t_begin <= t <= (self.t_end or t):
+                    clocks.append(clk)
+                    for bit, name in self.REASONS.items():
+                        if mask & bit and name != "gpu_idle":
+                            reasons.add(name)
+        s_ = sorted(clocks)
+        return {"sm_mhz": s_[len(s_) // 2] if s_ else None, "sm_max_mhz": sm_max, "reasons": sorted(reasons),
+                "samples": len(s_)}
 
 
 # ------------------------------------------------------------------------------------------------
@@ -427,8 +452,10 @@ def run_gpu_arm(args, rank: int, world: int, local_rank: int):
         if sampler:
             sampler.active = True
         start.record()
+        host_t = [time.perf_counter()]
         for i in range(args.steps):
             gathered = step(i, ev[i])
+            host_t.append(time.perf_counter())
         if world > 1:
             torch.cuda.current_stream(dev).wait_event(gathered)  # every all-gather ends inside the timed region
         end.record()
@@ -440,6 +467,7 @@ def run_gpu_arm(args, rank: int, world: int, local_rank: int):
         clocks = sampler.stop() if sampler else None
         m.vq.check_errors()
     elapsed_ms = start.elapsed_time(end)
+    log("[bench] per-step host enqueue ms: " + " ".join(f"{(b - a) * 1e3:.3f}" for a, b in zip(host_t, host_t[1:])))
     log("[bench] per-step encode ms: " + " ".join(f"{e[0].elapsed_time(e[1]):.3f}" for e in ev))
     enc_ms = sum(e[0].elapsed_time(e[1]) for e in ev) / args.steps
     dec_ms = sum(e[1].elapsed_time(e[2]) for e in ev) / args.steps

@@ -176,6 +176,17 @@ int stream_wait_flags(const char *who, unsigned char *mine, bool acks, int W, in
 
 }  // namespace
 
+__global__ void gate_kernel(const volatile int *flag, long long timeout_ns) {
+    const long long t0 = now_ns();
+    while (*flag == 0 && now_ns() - t0 < timeout_ns) __nanosleep(500);
+}
+
+extern "C" int rvq_debug_gate(const int *host_mapped_flag, int64_t timeout_ns, void *stream) {
+    RVQ_REQUIRE(host_mapped_flag && timeout_ns > 0 && timeout_ns <= 2000000000LL, RVQ_EINVAL, "rvq_debug_gate: bad arguments");
+    gate_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(host_mapped_flag, timeout_ns);
+    return rvq_check_launch("rvq_debug_gate");
+}
+
 extern "C" int64_t rvq_exchange_header_bytes(void) { return FLAG_BYTES; }
 
 extern "C" int rvq_exchange_push(void *const *peer_base, int W, int rank, int slot, int nslots, uint32_t seq,

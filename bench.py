@@ -400,15 +400,21 @@ def run_gpu_arm(args, rank: int, world: int, local_rank: int):
             dist.barrier()
         torch.cuda.synchronize(dev)
         if settle and world > 1:
-            # The ranks leave the barrier a millisecond or two apart (host wake-up), and the code exchange couples
-            # them with two steps of slack: the rank that starts first then waits for the last one inside the timed
-            # region.  Agree on a wall-clock start (one host, one clock) and spin up to it.
-            t0 = torch.tensor([time.time() + 0.02], dtype=torch.float64, device=dev)
-            dist.all_reduce(t0, op=dist.ReduceOp.MAX)
-            t_start = float(t0.item())
-            torch.cuda.synchronize(dev)
-            while time.time() < t_start:
-                pass
+            # After an idle spell the GPUs of the ranks begin to execute a millisecond or two apart, and the code
+            # exchange couples the ranks: whoever starts first then waits for the last one inside the timed region.
+            # So every rank parks its stream behind a gate kernel (the GPU is awake, nothing else runs), the ranks
+            # agree on a wall-clock time (one host, one clock), and each host opens its gate at that time.  The timed
+            # region -- start event, K steps, end event -- is enqueued behind the gate.
+            from audiocraft_b200 import _lib as rvq_lib
+            gate = torch.zeros(1, dtype=torch.int32).pin_memory()
+            rc = rvq_lib.load().rvq_debug_gate(gate.data_ptr(), int(1e9), torch.cuda.current_stream(dev).cuda_stream)
+            rvq_lib.check(rc, "rvq_debug_gate")
+            t0 = torch.tensor([time.time() + 0.01], dtype=torch.float64)
+            dist.all_reduce(t0, op=dist.ReduceOp.MAX, group=gate_group)
+            return gate, float(t0.item())
+        return None, None
+
+    gate_group = dist.new_group(backend="gloo") if world > 1 else None  # host-side agreement, no GPU work
 
     # ---- device-resident timing -------------------------------------------------------------
     with torch.no_grad():
@@ -441,21 +447,24 @@ def run_gpu_arm(args, rank: int, world: int, local_rank: int):
             for e in e3:
                 e.record()
         start.record(); end.record()
-        sync_all(settle=True)
-        if os.environ.get("BENCH_PING") and world > 1:
-            step(0)
-            torch.cuda.synchronize(dev)
+        gate, t_open = sync_all(settle=True)
         import gc
         gc.collect()
         gc.disable()
         kernels.launch_count(reset=True)
         if sampler:
             sampler.active = True
-        start.record()
+        start.record()          # behind the gate when there is one
         host_t = [time.perf_counter()]
         for i in range(args.steps):
             gathered = step(i, ev[i])
             host_t.append(time.perf_counter())
+            if gate is not None and i == min(1, args.steps - 1):
+                # two steps are queued behind the gate: open it at the agreed time (the host keeps ahead of the GPU)
+                while time.time() < t_open:
+                    pass
+                gate[0] = 1
+                gate = None
         if world > 1:
             torch.cuda.current_stream(dev).wait_event(gathered)  # every all-gather ends inside the timed region
         end.record()

@@ -245,6 +245,12 @@ int rvq_debug_tc_scores(const float *x, const int64_t xs[3], int B, int D, int T
                         int Ktot, int C, int K, int stage, int64_t *codes, float *acc_out,
                         float *info_out, void *workspace, int64_t workspace_bytes, void *stream);
 
+/* Measurement aid (no counterpart in the reference): one thread spins on the stream until *host_mapped_flag (an int
+ * in pinned, device-visible host memory) becomes non-zero or timeout_ns (at most 2 s) pass.  bench.py starts the
+ * timed region of every rank behind such a gate, opened at an agreed wall-clock time: the GPUs are awake and start
+ * together (after an idle spell they begin to execute a millisecond or two apart otherwise). */
+int rvq_debug_gate(const int *host_mapped_flag, int64_t timeout_ns, void *stream);
+
 /* Introspection used by tests and the bench: number of kernels launched by this library on the
  * calling thread since the last reset (the bench's `gpu_launches`). */
 int64_t rvq_b200_launch_count(int reset);

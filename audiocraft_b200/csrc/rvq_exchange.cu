@@ -24,7 +24,10 @@
 namespace {
 
 constexpr int MAXW = 16;
-constexpr int TPB = 256;
+// One warp of at most 32 registers per block: such a block fits on an SM beside a CTA of the persistent encode kernel
+// (384 threads x 168 registers leave exactly 1024 registers), so the exchange neither waits for a whole encode to
+// retire nor keeps an encode CTA off its SM.
+constexpr int TPB = 32;
 constexpr int64_t FLAG_BYTES = 16384;  // data flags in the first half, acknowledgements in the second
 constexpr int64_t ACK_OFFSET = FLAG_BYTES / 2;
 constexpr long long TIMEOUT_NS = 50LL * 1000 * 1000;
@@ -88,7 +91,7 @@ __device__ __forceinline__ bool last_block(unsigned int *ticket) {
     return last != 0;
 }
 
-__global__ void __launch_bounds__(TPB) push_kernel(Peers peers, int W, int rank, int slot, int nslots, uint32_t seq,
+__global__ void __maxnreg__(32) push_kernel(Peers peers, int W, int rank, int slot, int nslots, uint32_t seq,
                                                    int64_t slot_bytes, int64_t shard_bytes, unsigned int *ticket,
                                                    int64_t *status, int spin) {
     unsigned char *mine = peers.base[rank];
@@ -111,7 +114,7 @@ __device__ __forceinline__ void shard_of(int c, int base, int extra, int &r, int
     else { const int d = c - big; r = extra + d / base; off = d - (r - extra) * base; }
 }
 
-__global__ void __launch_bounds__(TPB) widen_wait_kernel(Peers peers, int W, int rank, int slot, uint32_t seq, int64_t slot_bytes,
+__global__ void __maxnreg__(32) widen_wait_kernel(Peers peers, int W, int rank, int slot, uint32_t seq, int64_t slot_bytes,
                                                          int64_t shard_bytes, int K, int B, int T, int axis,
                                                          int64_t *__restrict__ out, unsigned int *ticket, int64_t *status, int spin) {
     unsigned char *mine = peers.base[rank];
@@ -199,8 +202,8 @@ extern "C" int rvq_exchange_push(void *const *peer_base, int W, int rank, int sl
                     shard_bytes % 16 == 0 && slot_bytes >= (int64_t)W * shard_bytes && slot_bytes % 16 == 0 && scratch && status,
                 RVQ_EINVAL, "rvq_exchange_push: bad slot geometry");
     const int64_t n16 = shard_bytes / 16;
-    int64_t blocks = (n16 + TPB * 4 - 1) / (TPB * 4);
-    if (blocks > 32) blocks = 32;  // a few SMs' worth: NVLink, not the SMs, carries this
+    int64_t blocks = (n16 + TPB * 8 - 1) / (TPB * 8);
+    if (blocks > 148) blocks = 148;  // one small block per SM
     if (blocks < 1) blocks = 1;
     const int spin = spin_wait ? 1 : 0;
     if (!spin) {
@@ -224,8 +227,8 @@ extern "C" int rvq_exchange_widen(void *const *peer_base, int W, int rank, int s
                     codes && scratch && status && (axis == 0 ? B : T) >= W,
                 RVQ_EINVAL, "rvq_exchange_widen: bad arguments");
     const int64_t total = (int64_t)K * B * T;
-    int64_t blocks = (total + TPB * 8 - 1) / (TPB * 8);
-    if (blocks > 148 * 4) blocks = 148 * 4;
+    int64_t blocks = (total + TPB * 16 - 1) / (TPB * 16);
+    if (blocks > 148 * 2) blocks = 148 * 2;
     if (blocks < 1) blocks = 1;
     const int spin = spin_wait ? 1 : 0;
     if (!spin) {

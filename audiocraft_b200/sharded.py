@@ -15,6 +15,7 @@ frame -- so any split of the B*T frames is valid: no halo, no exchange during co
 """
 from __future__ import annotations
 
+import os
 import typing as tp
 
 import torch
@@ -219,7 +220,13 @@ class ShardedRVQ:
             if out is None:
                 out = torch.empty((K, B, T), dtype=torch.int64, device=dev)
             stream = torch.cuda.current_stream(dev).cuda_stream
-            spin = st.get("spin", False)
+            # in-kernel waits by default: the exchange kernels are single warps of 32 registers that sit beside the encode
+            # kernel's CTAs, and they notice a flag within microseconds (a stream memory operation can take milliseconds
+            # to be re-examined when the GPU is busy); RVQ_EXCHANGE_STREAM_WAIT=1 selects the stream operations
+            spin = st.get("spin", os.environ.get("RVQ_EXCHANGE_STREAM_WAIT") != "1")
+            trace = getattr(self, "trace", None)
+            if trace is not None:
+                e0 = torch.cuda.Event(enable_timing=True); e0.record(torch.cuda.current_stream(dev))
             try:
                 kernels.exchange_push(st["geo"], st["ptrs"], self.rank, bufs["seq"], st["scratch"], st["status"], stream,
                                       spin_wait=spin)
@@ -230,8 +237,13 @@ class ShardedRVQ:
                 spin = st["spin"] = True
                 kernels.exchange_push(st["geo"], st["ptrs"], self.rank, bufs["seq"], st["scratch"], st["status"], stream,
                                       spin_wait=True)
+            if trace is not None:
+                e1 = torch.cuda.Event(enable_timing=True); e1.record(torch.cuda.current_stream(dev))
             kernels.exchange_widen(st["geo"], st["ptrs"], self.rank, bufs["seq"], out, st["scratch"], st["status"], stream,
                                    spin_wait=spin)
+            if trace is not None:
+                e2 = torch.cuda.Event(enable_timing=True); e2.record(torch.cuda.current_stream(dev))
+                trace.append((e0, e1, e2))
             ev = torch.cuda.Event()
             ev.record(torch.cuda.current_stream(dev))
             st["free"][bufs["seq"] % st["geo"].nslots] = ev

@@ -454,6 +454,8 @@ def run_gpu_arm(args, rank: int, world: int, local_rank: int):
         kernels.launch_count(reset=True)
         if sampler:
             sampler.active = True
+        if sharded is not None and os.environ.get("BENCH_TRACE"):
+            sharded.trace = []
         start.record()          # behind the gate when there is one
         host_t = [time.perf_counter()]
         for i in range(args.steps):
@@ -476,6 +478,9 @@ def run_gpu_arm(args, rank: int, world: int, local_rank: int):
         clocks = sampler.stop() if sampler else None
         m.vq.check_errors()
     elapsed_ms = start.elapsed_time(end)
+    if sharded is not None and getattr(sharded, "trace", None):
+        log("[bench] gather trace (start after timed start, push ms, widen ms): " + " ".join(
+            f"{start.elapsed_time(a):.2f}/{a.elapsed_time(b):.2f}/{b.elapsed_time(c):.2f}" for a, b, c in sharded.trace))
     log("[bench] per-step host enqueue ms: " + " ".join(f"{(b - a) * 1e3:.3f}" for a, b in zip(host_t, host_t[1:])))
     log("[bench] per-step encode ms: " + " ".join(f"{e[0].elapsed_time(e[1]):.3f}" for e in ev))
     enc_ms = sum(e[0].elapsed_time(e[1]) for e in ev) / args.steps

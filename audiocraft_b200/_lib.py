@@ -39,6 +39,7 @@ SIGNATURES = {
     "rvq_widen_codes_i16": (_i32, [_vp, _i32, _i32, _i32, _i32, _i32, _vp, _vp]),
     "rvq_exchange_header_bytes": (_i64, []),
     "rvq_debug_gate": (_i32, [_vp, _i64, _vp]),
+    "rvq_b200_set_reserved_sms": (_i32, [_i32]),
     "rvq_exchange_push": (_i32, [ctypes.POINTER(_vp), _i32, _i32, _i32, _i32, ctypes.c_uint32, _i64, _i64, _vp, _vp, _i32,
                                  _vp]),
     "rvq_exchange_widen": (_i32, [ctypes.POINTER(_vp), _i32, _i32, _i32, _i32, ctypes.c_uint32, _i64, _i64, _i32, _i32, _i32,

@@ -1013,10 +1013,21 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
 // ------------------------------------------------------------------------------------ host
 bool rvq_tc_shape_supported(int D, int C) { return D == 128 && C % 128 == 0 && C >= 256 && C <= 16384; }
 
+// SMs the persistent encode kernel leaves free (process-wide setting, rvq_b200_set_reserved_sms): a frame-sharded job
+// keeps a few for the kernels of its code exchange, which otherwise find room only between two encodes.
+static int g_reserved_sms = 0;
+
+extern "C" int rvq_b200_set_reserved_sms(int n) {
+    RVQ_REQUIRE(n >= 0 && n <= 64, RVQ_EINVAL, "rvq_b200_set_reserved_sms: %d is not in [0, 64]", n);
+    g_reserved_sms = n;
+    return RVQ_OK;
+}
+
 static int device_sms(int *sms) {
     int dev = 0;
     RVQ_CUDA(cudaGetDevice(&dev));
     RVQ_CUDA(cudaDeviceGetAttribute(sms, cudaDevAttrMultiProcessorCount, dev));
+    if (*sms - g_reserved_sms >= 8) *sms -= g_reserved_sms;
     return RVQ_OK;
 }
 

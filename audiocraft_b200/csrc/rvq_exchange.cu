@@ -121,17 +121,36 @@ __global__ void __maxnreg__(32) widen_wait_kernel(Peers peers, int W, int rank, 
     if (spin) wait_flags(false, mine, W, slot, seq, status, 2);
     const unsigned char *slot_base = mine + FLAG_BYTES + (int64_t)slot * slot_bytes;
     const int n = axis == 0 ? B : T, base = n / W, extra = n % W, smax = base + (extra ? 1 : 0);
-    const int64_t total = (int64_t)K * B * T;
-    for (int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x; i < total; i += (int64_t)gridDim.x * TPB) {
-        const int t = (int)(i % T), b = (int)((i / T) % B), k = (int)(i / ((int64_t)T * B));
-        int r, off;
-        int64_t src;
-        if (axis == 0) { shard_of(b, base, extra, r, off); src = ((int64_t)k * smax + off) * T + t; }
-        else { shard_of(t, base, extra, r, off); src = ((int64_t)k * B + b) * smax + off; }
-        out[i] = (int64_t)reinterpret_cast<const int16_t *>(slot_base + (int64_t)r * shard_bytes)[src];
+    // one warp per row (k, b): the time axis is contiguous on both sides, no division per element
+    const int64_t rows = (int64_t)K * B;
+    for (int64_t row = blockIdx.x; row < rows; row += gridDim.x) {
+        const int b = (int)(row % B), k = (int)(row / B);
+        int64_t *dst = out + row * T;
+        if (axis == 0) {
+            int r, off;
+            shard_of(b, base, extra, r, off);
+            const int16_t *src = reinterpret_cast<const int16_t *>(slot_base + (int64_t)r * shard_bytes) + ((int64_t)k * smax + off) * T;
+            for (int t = threadIdx.x; t < T; t += TPB) dst[t] = (int64_t)src[t];
+        } else {
+            int lo = 0;
+            for (int r = 0; r < W; ++r) {
+                const int len = base + (r < extra ? 1 : 0);
+                const int16_t *src = reinterpret_cast<const int16_t *>(slot_base + (int64_t)r * shard_bytes) + ((int64_t)k * B + b) * smax;
+                for (int t = threadIdx.x; t < len; t += TPB) dst[lo + t] = (int64_t)src[t];
+                lo += len;
+            }
+        }
     }
     if (last_block(ticket) && (int)threadIdx.x < W)
         st_release_sys(ack_flag(peers.base[threadIdx.x], W, slot, rank), seq);
+}
+
+// The exchange kernels want the same shared-memory / L1 split as the encode kernel (all shared memory): an SM runs
+// blocks of two kernels side by side only when they agree on that split.
+template <typename KernelT>
+int prefer_max_shared(KernelT kern) {
+    RVQ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared));
+    return RVQ_OK;
 }
 
 int fill_peers(const char *who, void *const *peer_base, int W, int rank, Peers &p) {
@@ -203,8 +222,10 @@ extern "C" int rvq_exchange_push(void *const *peer_base, int W, int rank, int sl
                 RVQ_EINVAL, "rvq_exchange_push: bad slot geometry");
     const int64_t n16 = shard_bytes / 16;
     int64_t blocks = (n16 + TPB * 8 - 1) / (TPB * 8);
-    if (blocks > 148) blocks = 148;  // one small block per SM
+    if (blocks > 64) blocks = 64;  // few enough to be resident together on the SMs a sharded job keeps free (4 x 16)
     if (blocks < 1) blocks = 1;
+    static const int carve_push = prefer_max_shared(push_kernel);
+    if (carve_push != RVQ_OK) return carve_push;
     const int spin = spin_wait ? 1 : 0;
     if (!spin) {
         rc = stream_wait_flags("rvq_exchange_push", p.base[rank], true, W, rank, slot,
@@ -228,8 +249,10 @@ extern "C" int rvq_exchange_widen(void *const *peer_base, int W, int rank, int s
                 RVQ_EINVAL, "rvq_exchange_widen: bad arguments");
     const int64_t total = (int64_t)K * B * T;
     int64_t blocks = (total + TPB * 16 - 1) / (TPB * 16);
-    if (blocks > 148 * 2) blocks = 148 * 2;
+    if (blocks > 64) blocks = 64;  // as above: every block must be able to start at once (they all wait for the flags)
     if (blocks < 1) blocks = 1;
+    static const int carve_widen = prefer_max_shared(widen_wait_kernel);
+    if (carve_widen != RVQ_OK) return carve_widen;
     const int spin = spin_wait ? 1 : 0;
     if (!spin) {
         rc = stream_wait_flags("rvq_exchange_widen", p.base[rank], false, W, rank, slot, seq, (cudaStream_t)stream);

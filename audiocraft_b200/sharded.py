@@ -60,6 +60,11 @@ class ShardedRVQ:
         assert exchange in ("auto", "p2p", "nccl")
         self.exchange = exchange
         self._p2p: tp.Dict[tuple, tp.Any] = {}
+        if self.world > 1 and torch.cuda.is_available():
+            # the persistent encode kernel leaves four SMs to the exchange kernels (config 2's 750 tiles take three
+            # rounds on 144 CTAs as on 148: nothing is lost)
+            from . import _lib
+            _lib.check(_lib.load().rvq_b200_set_reserved_sms(int(os.environ.get("RVQ_RESERVED_SMS", "4"))), "rvq_b200_set_reserved_sms")
         if self.world > 1 and hasattr(quantizer, "buffers"):
             for buf in quantizer.buffers():
                 dist.broadcast(buf, src=0, group=group)

@@ -409,10 +409,14 @@ def run_gpu_arm(args, rank: int, world: int, local_rank: int):
             gate = torch.zeros(1, dtype=torch.int32).pin_memory()
             rc = rvq_lib.load().rvq_debug_gate(gate.data_ptr(), int(1e9), torch.cuda.current_stream(dev).cuda_stream)
             rvq_lib.check(rc, "rvq_debug_gate")
-            t0 = torch.tensor([time.time() + 0.01], dtype=torch.float64)
-            dist.all_reduce(t0, op=dist.ReduceOp.MAX, group=gate_group)
-            return gate, float(t0.item())
-        return None, None
+            return gate
+        return None
+
+    def agree_on_opening_time():
+        """Called when everything but the enqueueing of the steps is done: a wall-clock time 10 ms from the latest rank."""
+        t0 = torch.tensor([time.time() + 0.01], dtype=torch.float64)
+        dist.all_reduce(t0, op=dist.ReduceOp.MAX, group=gate_group)
+        return float(t0.item())
 
     gate_group = dist.new_group(backend="gloo") if world > 1 else None  # host-side agreement, no GPU work
 
@@ -447,7 +451,7 @@ def run_gpu_arm(args, rank: int, world: int, local_rank: int):
             for e in e3:
                 e.record()
         start.record(); end.record()
-        gate, t_open = sync_all(settle=True)
+        gate = sync_all(settle=True)
         import gc
         gc.collect()
         gc.disable()
@@ -456,6 +460,7 @@ def run_gpu_arm(args, rank: int, world: int, local_rank: int):
             sampler.active = True
         if sharded is not None and os.environ.get("BENCH_TRACE"):
             sharded.trace = []
+        t_open = agree_on_opening_time() if gate is not None else None
         start.record()          # behind the gate when there is one
         host_t = [time.perf_counter()]
         for i in range(args.steps):

@@ -245,6 +245,12 @@ int rvq_debug_tc_scores(const float *x, const int64_t xs[3], int B, int D, int T
                         int Ktot, int C, int K, int stage, int64_t *codes, float *acc_out,
                         float *info_out, void *workspace, int64_t workspace_bytes, void *stream);
 
+/* The tensor-core encode kernel is persistent, one CTA per SM, and each CTA takes its SM whole.  A frame-sharded job
+ * sets aside `n` SMs (0..64, process-wide, default 0) for the small kernels of its code exchange, which could otherwise
+ * only run in the gap between two encodes.  Takes effect at the next rvq_encode_workspace_bytes / rvq_encode_f32 pair
+ * (call it before sizing the workspace).  No counterpart in the reference. */
+int rvq_b200_set_reserved_sms(int n);
+
 /* Measurement aid (no counterpart in the reference): one thread spins on the stream until *host_mapped_flag (an int
  * in pinned, device-visible host memory) becomes non-zero or timeout_ns (at most 2 s) pass.  bench.py starts the
  * timed region of every rank behind such a gate, opened at an agreed wall-clock time: the GPUs are awake and start

@@ -399,7 +399,7 @@ def run_gpu_arm(args, rank: int, world: int, local_rank: int):
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize(dev)
-        if settle and world > 1:
+        if settle:
             # After an idle spell the GPUs of the ranks begin to execute a millisecond or two apart, and the code
             # exchange couples the ranks: whoever starts first then waits for the last one inside the timed region.
             # So every rank parks its stream behind a gate kernel (the GPU is awake, nothing else runs), the ranks
@@ -415,7 +415,8 @@ def run_gpu_arm(args, rank: int, world: int, local_rank: int):
     def agree_on_opening_time():
         """Called when everything but the enqueueing of the steps is done: a wall-clock time 10 ms from the latest rank."""
         t0 = torch.tensor([time.time() + 0.01], dtype=torch.float64)
-        dist.all_reduce(t0, op=dist.ReduceOp.MAX, group=gate_group)
+        if world > 1:
+            dist.all_reduce(t0, op=dist.ReduceOp.MAX, group=gate_group)
         return float(t0.item())
 
     gate_group = dist.new_group(backend="gloo") if world > 1 else None  # host-side agreement, no GPU work

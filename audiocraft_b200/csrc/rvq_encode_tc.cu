@@ -1023,6 +1023,8 @@ extern "C" int rvq_b200_set_reserved_sms(int n) {
     return RVQ_OK;
 }
 
+int rvq_reserved_sms() { return g_reserved_sms; }
+
 static int device_sms(int *sms) {
     int dev = 0;
     RVQ_CUDA(cudaGetDevice(&dev));

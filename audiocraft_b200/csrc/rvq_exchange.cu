@@ -21,13 +21,16 @@
 
 #include "rvq_common.cuh"
 
+int rvq_reserved_sms();  // rvq_encode_tc.cu
+
 namespace {
 
 constexpr int MAXW = 16;
-// One warp of at most 32 registers per block: such a block fits on an SM beside a CTA of the persistent encode kernel
-// (384 threads x 168 registers leave exactly 1024 registers), so the exchange neither waits for a whole encode to
-// retire nor keeps an encode CTA off its SM.
-constexpr int TPB = 32;
+// The exchange kernels run on the SMs a sharded job keeps free of the persistent encode kernel
+// (rvq_b200_set_reserved_sms): few enough blocks that all of them are resident at once, since every block waits for
+// the flags before it starts to work.
+constexpr int TPB = 256;
+constexpr int BLOCKS_PER_SM = 8;
 constexpr int64_t FLAG_BYTES = 16384;  // data flags in the first half, acknowledgements in the second
 constexpr int64_t ACK_OFFSET = FLAG_BYTES / 2;
 constexpr long long TIMEOUT_NS = 50LL * 1000 * 1000;
@@ -91,7 +94,7 @@ __device__ __forceinline__ bool last_block(unsigned int *ticket) {
     return last != 0;
 }
 
-__global__ void __maxnreg__(32) push_kernel(Peers peers, int W, int rank, int slot, int nslots, uint32_t seq,
+__global__ void __launch_bounds__(TPB) push_kernel(Peers peers, int W, int rank, int slot, int nslots, uint32_t seq,
                                                    int64_t slot_bytes, int64_t shard_bytes, unsigned int *ticket,
                                                    int64_t *status, int spin) {
     unsigned char *mine = peers.base[rank];
@@ -102,7 +105,16 @@ __global__ void __maxnreg__(32) push_kernel(Peers peers, int W, int rank, int sl
     for (int p = 0; p < W; ++p) {
         if (p == rank) continue;  // my own shard is already in place: the encode kernel wrote it there
         uint4 *dst = reinterpret_cast<uint4 *>(peers.base[p] + off);
-        for (int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x; i < n16; i += (int64_t)gridDim.x * TPB) dst[i] = src[i];
+        const int64_t stride = (int64_t)gridDim.x * TPB;
+        for (int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x; i < n16; i += 4 * stride) {
+            uint4 v[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+                if (i + j * stride < n16) v[j] = src[i + j * stride];
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+                if (i + j * stride < n16) dst[i + j * stride] = v[j];
+        }
     }
     if (last_block(ticket) && (int)threadIdx.x < W)
         st_release_sys(data_flag(peers.base[threadIdx.x], W, slot, rank), seq);
@@ -114,7 +126,24 @@ __device__ __forceinline__ void shard_of(int c, int base, int extra, int &r, int
     else { const int d = c - big; r = extra + d / base; off = d - (r - extra) * base; }
 }
 
-__global__ void __maxnreg__(32) widen_wait_kernel(Peers peers, int W, int rank, int slot, uint32_t seq, int64_t slot_bytes,
+// len int16 -> int64, one warp; four elements per lane and step when both sides are aligned for it
+__device__ __forceinline__ void widen_row(int64_t *dst, const int16_t *src, int len, int lane) {
+    if ((((uintptr_t)src & 7) | ((uintptr_t)dst & 15)) == 0) {
+        const int n4 = len / 4;
+        for (int i = lane; i < n4; i += 32) {
+            const short4 v = reinterpret_cast<const short4 *>(src)[i];
+            longlong2 a, c;
+            a.x = v.x; a.y = v.y; c.x = v.z; c.y = v.w;
+            reinterpret_cast<longlong2 *>(dst)[2 * i] = a;
+            reinterpret_cast<longlong2 *>(dst)[2 * i + 1] = c;
+        }
+        for (int t = n4 * 4 + lane; t < len; t += 32) dst[t] = (int64_t)src[t];
+    } else {
+        for (int t = lane; t < len; t += 32) dst[t] = (int64_t)src[t];
+    }
+}
+
+__global__ void __launch_bounds__(TPB) widen_wait_kernel(Peers peers, int W, int rank, int slot, uint32_t seq, int64_t slot_bytes,
                                                          int64_t shard_bytes, int K, int B, int T, int axis,
                                                          int64_t *__restrict__ out, unsigned int *ticket, int64_t *status, int spin) {
     unsigned char *mine = peers.base[rank];
@@ -123,20 +152,21 @@ __global__ void __maxnreg__(32) widen_wait_kernel(Peers peers, int W, int rank, 
     const int n = axis == 0 ? B : T, base = n / W, extra = n % W, smax = base + (extra ? 1 : 0);
     // one warp per row (k, b): the time axis is contiguous on both sides, no division per element
     const int64_t rows = (int64_t)K * B;
-    for (int64_t row = blockIdx.x; row < rows; row += gridDim.x) {
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5, wpb = TPB / 32;
+    for (int64_t row = (int64_t)blockIdx.x * wpb + wib; row < rows; row += (int64_t)gridDim.x * wpb) {
         const int b = (int)(row % B), k = (int)(row / B);
         int64_t *dst = out + row * T;
         if (axis == 0) {
             int r, off;
             shard_of(b, base, extra, r, off);
             const int16_t *src = reinterpret_cast<const int16_t *>(slot_base + (int64_t)r * shard_bytes) + ((int64_t)k * smax + off) * T;
-            for (int t = threadIdx.x; t < T; t += TPB) dst[t] = (int64_t)src[t];
+            widen_row(dst, src, T, lane);
         } else {
             int lo = 0;
             for (int r = 0; r < W; ++r) {
                 const int len = base + (r < extra ? 1 : 0);
                 const int16_t *src = reinterpret_cast<const int16_t *>(slot_base + (int64_t)r * shard_bytes) + ((int64_t)k * B + b) * smax;
-                for (int t = threadIdx.x; t < len; t += TPB) dst[lo + t] = (int64_t)src[t];
+                widen_row(dst + lo, src, len, lane);
                 lo += len;
             }
         }
@@ -145,12 +175,9 @@ __global__ void __maxnreg__(32) widen_wait_kernel(Peers peers, int W, int rank, 
         st_release_sys(ack_flag(peers.base[threadIdx.x], W, slot, rank), seq);
 }
 
-// The exchange kernels want the same shared-memory / L1 split as the encode kernel (all shared memory): an SM runs
-// blocks of two kernels side by side only when they agree on that split.
-template <typename KernelT>
-int prefer_max_shared(KernelT kern) {
-    RVQ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared));
-    return RVQ_OK;
+int64_t exchange_blocks() {
+    const int sms = rvq_reserved_sms();
+    return (int64_t)(sms > 0 ? sms : 4) * BLOCKS_PER_SM;
 }
 
 int fill_peers(const char *who, void *const *peer_base, int W, int rank, Peers &p) {
@@ -221,11 +248,10 @@ extern "C" int rvq_exchange_push(void *const *peer_base, int W, int rank, int sl
                     shard_bytes % 16 == 0 && slot_bytes >= (int64_t)W * shard_bytes && slot_bytes % 16 == 0 && scratch && status,
                 RVQ_EINVAL, "rvq_exchange_push: bad slot geometry");
     const int64_t n16 = shard_bytes / 16;
-    int64_t blocks = (n16 + TPB * 8 - 1) / (TPB * 8);
-    if (blocks > 64) blocks = 64;  // few enough to be resident together on the SMs a sharded job keeps free (4 x 16)
+    int64_t blocks = (n16 + TPB * 4 - 1) / (TPB * 4);
+    const int64_t cap = exchange_blocks();
+    if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
-    static const int carve_push = prefer_max_shared(push_kernel);
-    if (carve_push != RVQ_OK) return carve_push;
     const int spin = spin_wait ? 1 : 0;
     if (!spin) {
         rc = stream_wait_flags("rvq_exchange_push", p.base[rank], true, W, rank, slot,
@@ -248,11 +274,10 @@ extern "C" int rvq_exchange_widen(void *const *peer_base, int W, int rank, int s
                     codes && scratch && status && (axis == 0 ? B : T) >= W,
                 RVQ_EINVAL, "rvq_exchange_widen: bad arguments");
     const int64_t total = (int64_t)K * B * T;
-    int64_t blocks = (total + TPB * 16 - 1) / (TPB * 16);
-    if (blocks > 64) blocks = 64;  // as above: every block must be able to start at once (they all wait for the flags)
+    int64_t blocks = ((int64_t)K * B + TPB / 32 - 1) / (TPB / 32);
+    const int64_t cap = exchange_blocks();
+    if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
-    static const int carve_widen = prefer_max_shared(widen_wait_kernel);
-    if (carve_widen != RVQ_OK) return carve_widen;
     const int spin = spin_wait ? 1 : 0;
     if (!spin) {
         rc = stream_wait_flags("rvq_exchange_widen", p.base[rank], false, W, rank, slot, seq, (cudaStream_t)stream);

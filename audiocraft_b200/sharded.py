@@ -61,10 +61,11 @@ class ShardedRVQ:
         self.exchange = exchange
         self._p2p: tp.Dict[tuple, tp.Any] = {}
         if self.world > 1 and torch.cuda.is_available():
-            # the persistent encode kernel leaves four SMs to the exchange kernels (config 2's 750 tiles take three
-            # rounds on 144 CTAs as on 148: nothing is lost)
+            # the persistent encode kernel leaves a few SMs to the exchange kernels (config 2's 750 tiles take three
+            # rounds on 140 CTAs as on 148: nothing is lost); more ranks move more bytes per step
             from . import _lib
-            _lib.check(_lib.load().rvq_b200_set_reserved_sms(int(os.environ.get("RVQ_RESERVED_SMS", "4"))), "rvq_b200_set_reserved_sms")
+            n = int(os.environ.get("RVQ_RESERVED_SMS", "4" if self.world <= 2 else "8"))
+            _lib.check(_lib.load().rvq_b200_set_reserved_sms(n), "rvq_b200_set_reserved_sms")
         if self.world > 1 and hasattr(quantizer, "buffers"):
             for buf in quantizer.buffers():
                 dist.broadcast(buf, src=0, group=group)
@@ -225,9 +226,8 @@ class ShardedRVQ:
             if out is None:
                 out = torch.empty((K, B, T), dtype=torch.int64, device=dev)
             stream = torch.cuda.current_stream(dev).cuda_stream
-            # in-kernel waits by default: the exchange kernels are single warps of 32 registers that sit beside the encode
-            # kernel's CTAs, and they notice a flag within microseconds (a stream memory operation can take milliseconds
-            # to be re-examined when the GPU is busy); RVQ_EXCHANGE_STREAM_WAIT=1 selects the stream operations
+            # in-kernel waits by default: the exchange kernels run on the SMs the encode kernel leaves free and notice a
+            # flag within microseconds; RVQ_EXCHANGE_STREAM_WAIT=1 selects stream memory operations instead
             spin = st.get("spin", os.environ.get("RVQ_EXCHANGE_STREAM_WAIT") != "1")
             trace = getattr(self, "trace", None)
             if trace is not None:

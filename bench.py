@@ -399,7 +399,8 @@ def run_gpu_arm(args, rank: int, world: int, local_rank: int):
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize(dev)
-        if settle:
+        if settle and not os.environ.get("BENCH_NO_GATE"):
+            # (BENCH_NO_GATE=1: for runs under ncu, which serialises launches)
             # After an idle spell the GPUs of the ranks begin to execute a millisecond or two apart, and the code
             # exchange couples the ranks: whoever starts first then waits for the last one inside the timed region.
             # So every rank parks its stream behind a gate kernel (the GPU is awake, nothing else runs), the ranks
@@ -586,7 +587,7 @@ def run_gpu_arm(args, rank: int, world: int, local_rank: int):
     achieved_tf = enc_flops / (enc_ms * 1e-3) / 1e12
     traffic = None
     try:  # DRAM bytes per launch of the encode kernel from the committed ncu --set full capture (profiles/)
-        with open(os.path.join(ROOT, "profiles", "r2_traffic.json")) as f:
+        with open(os.path.join(ROOT, "profiles", "r3_traffic.json")) as f:
             traffic = json.load(f).get("rvq_encode_tc_kernel_config2_bytes")
     except Exception:
         pass

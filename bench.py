@@ -8,7 +8,8 @@ A step = one pass of the hot path over one batch of synthetic latents: `encode(x
 i.e. through the C ABI.  At N = 1 the workload is BASELINE.json configs[1] (MusicGen 32 kHz RVQ,
 n_q=4 bins=2048 dim=128, B=64 x T=1500).  For N > 1 (torchrun, one rank per GPU) every rank
 encodes+decodes its own batch of that shape (frames are independent: weak scaling, no collective
-in the data path) and the codes are all-gathered with NCCL inside the timed region, as
+in the data path) and the codes of every step are exchanged between the ranks (peer stores into
+symmetric memory over NVLink, or one NCCL all-gather) inside the timed region, as
 BASELINE.json configs[4] describes.
 
 Rank 0 prints ONE JSON line.  `value` is frames/s of the whole job with inputs resident in HBM;
@@ -580,6 +581,10 @@ def run_gpu_arm(args, rank: int, world: int, local_rank: int):
             dist.destroy_process_group()
         return 0
 
+    exchange_kind = "none"
+    if sharded is not None:
+        exchange_kind = ("peer stores into symmetric memory + flags, librvq_b200.so kernels"
+                         if any(v is not None for v in sharded._p2p.values()) else "NCCL all_gather + one widening kernel")
     peaks = measured_peaks()
     total_frames = frames * world * args.steps
     value = total_frames / (elapsed_ms * 1e-3) / 1e6
@@ -627,7 +632,9 @@ def run_gpu_arm(args, rank: int, world: int, local_rank: int):
                    "l2": f"{N_ROTATING} rotating input batches ({N_ROTATING * h2d // 1000000} MB) > 126 MB L2",
                    "encode_algo": m.vq.encode_algo,
                    "untimed_steps_before_timing": args.warmup + 20 + int(extra.item()),
-                   "collective": "all_gather of the codes per step (int16 on the wire, side stream, all complete inside the timed region)" if world > 1 else "none"},
+                   "start": "timed region enqueued behind a gate kernel opened at an agreed wall-clock time",
+                   "collective": ("codes of every step exchanged as int16 (" + exchange_kind + "), side stream, all complete "
+                                  "inside the timed region") if world > 1 else "none"},
         "roofline": roofline,
         "cpu_baseline": cpu,
         "e2e": {"value": round(frames * world * args.steps / (e2e_ms * 1e-3) / 1e6, 4), "unit": UNIT,

@@ -250,6 +250,17 @@ __device__ __forceinline__ float transposed_butterfly8(float (&p)[8], int lane) 
     return v;
 }
 
+// The canonical combination of 32 lane partials (rvq_common.cuh: xor butterfly 16, 8, 4, 2, 1) when one thread
+// holds all of them: p[i] += p[i + half].  Same additions, same order, same bits.
+__device__ __forceinline__ float tree32(float (&p)[32]) {
+#pragma unroll
+    for (int half = 16; half >= 1; half >>= 1) {
+#pragma unroll
+        for (int i = 0; i < half; ++i) p[i] = __fadd_rn(p[i], p[i + half]);
+    }
+    return p[0];
+}
+
 __device__ __forceinline__ void warp_argmax(float &bs, int &bi) {
 #pragma unroll
     for (int off = 16; off >= 1; off >>= 1) {
@@ -572,42 +583,62 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
             const int64_t n_l = n0 + lane;
             const int64_t xoff = n_l < P.N ? (n_l / P.T) * P.xs_b + (n_l % P.T) * P.xs_t : -1;
             const int64_t woff = (P.wire.p && n_l < P.N) ? (n_l / P.T) * P.wire.sb + (n_l % P.T) : -1;
-            if (!direct) {
-                // lane = frame reads (coalesced when T is the contiguous axis), transposed 32 dims at a
-                // time through this warp's own 4 KB of the A tile into the scratch rows
-                float *st = reinterpret_cast<float *>(A + q * 4096);
-                float xv[32];  // the 32 loads of a pass in flight together, one pass ahead of the transposition
-#pragma unroll
-                for (int dd = 0; dd < 32; ++dd) xv[dd] = xoff >= 0 ? P.x[xoff + (int64_t)dd * P.xs_d] : 0.0f;
-#pragma unroll 1
-                for (int pass = 0; pass < 4; ++pass) {
-                    __syncwarp();
-#pragma unroll
-                    for (int dd = 0; dd < 32; ++dd) st[dd * 32 + (lane ^ dd)] = xv[dd];
-                    if (pass < 3) {
-#pragma unroll
-                        for (int dd = 0; dd < 32; ++dd)
-                            xv[dd] = xoff >= 0 ? P.x[xoff + (int64_t)((pass + 1) * 32 + dd) * P.xs_d] : 0.0f;
-                    }
-                    __syncwarp();
-#pragma unroll 8
-                    for (int f = 0; f < 32; ++f) rs[f * 128 + pass * 32 + lane] = st[lane * 32 + (f ^ lane)];
-                }
-                __syncwarp();
-            }
-
-            // ---- stage 0 operand rows; lane f keeps ||r_f||^2
             RvqStageMeta mt = P.meta[0];
             float xx = 0.0f;
-            {
-                // eight frames per iteration, the next eight requested before these are converted
+            if (!direct) {
+                // lane = frame reads (coalesced when T is the contiguous axis), the whole frame in flight.  The frame's
+                // own thread takes ||x||^2 (the canonical tree) and writes the stage 0 operand row; the fp32 rows go to
+                // the scratch transposed 32 dims at a time through this warp's own 4 KB of the A tile.
+                float *st = reinterpret_cast<float *>(A + q * 4096);
+                float v[4][32];
+#pragma unroll
+                for (int c = 0; c < 4; ++c)
+#pragma unroll
+                    for (int dd = 0; dd < 32; ++dd) v[c][dd] = xoff >= 0 ? P.x[xoff + (int64_t)(c * 32 + dd) * P.xs_d] : 0.0f;
+                float p[32];
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        float a = __fmaf_rn(v[c][4 * i], v[c][4 * i], 0.0f);
+                        a = __fmaf_rn(v[c][4 * i + 1], v[c][4 * i + 1], a);
+                        a = __fmaf_rn(v[c][4 * i + 2], v[c][4 * i + 2], a);
+                        p[8 * c + i] = __fmaf_rn(v[c][4 * i + 3], v[c][4 * i + 3], a);
+                    }
+                }
+                xx = tree32(p);
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    __syncwarp();
+#pragma unroll
+                    for (int dd = 0; dd < 32; ++dd) st[dd * 32 + (lane ^ dd)] = v[c][dd];
+                    __syncwarp();
+#pragma unroll 8
+                    for (int f = 0; f < 32; ++f) rs[f * 128 + c * 32 + lane] = st[lane * 32 + (f ^ lane)];
+                }
+                __syncwarp();
+                const FrameScale fs0 = frame_scale(xx, mt);
+                const float al = fs0.flags ? 0.0f : exp2i(fs0.ea);
+#pragma unroll
+                for (int c16 = 0; c16 < 16; ++c16) {  // 16-byte chunk = dims 8 c16 .. 8 c16 + 7
+                    __half2 h[4];
+#pragma unroll
+                    for (int i = 0; i < 4; ++i)
+                        h[i] = __floats2half2_rn(v[c16 >> 2][(c16 & 3) * 8 + 2 * i] * al, v[c16 >> 2][(c16 & 3) * 8 + 2 * i + 1] * al);
+                    uint4 w;
+                    w.x = *reinterpret_cast<const uint32_t *>(&h[0]);
+                    w.y = *reinterpret_cast<const uint32_t *>(&h[1]);
+                    w.z = *reinterpret_cast<const uint32_t *>(&h[2]);
+                    w.w = *reinterpret_cast<const uint32_t *>(&h[3]);
+                    *reinterpret_cast<uint4 *>(A + (c16 >> 3) * 16384 + row_l * 128 + (((c16 & 7) ^ (row_l & 7)) << 4)) = w;
+                }
+            } else {
+                // channels-last input: a frame is one 512-byte row; eight frames per iteration, the next eight requested
+                // before these are converted; lane f keeps ||r_f||^2
                 constexpr int NB = 8;
                 auto fetch = [&](int f) {
-                    if (direct) {
-                        const int64_t o = __shfl_sync(0xffffffffu, xoff, f);
-                        return o >= 0 ? *(reinterpret_cast<const float4 *>(P.x + o) + lane) : make_float4(0.f, 0.f, 0.f, 0.f);
-                    }
-                    return rs4[f * 32];
+                    const int64_t o = __shfl_sync(0xffffffffu, xoff, f);
+                    return o >= 0 ? *(reinterpret_cast<const float4 *>(P.x + o) + lane) : make_float4(0.f, 0.f, 0.f, 0.f);
                 };
                 float4 rf[NB];
 #pragma unroll
@@ -618,7 +649,7 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
 #pragma unroll
                     for (int t = 0; t < NB; ++t) {
                         cur[t] = rf[t];
-                        if (direct) rs4[(f0 + t) * 32] = cur[t];
+                        rs4[(f0 + t) * 32] = cur[t];
                     }
                     if (f0 + NB < 32) {
 #pragma unroll

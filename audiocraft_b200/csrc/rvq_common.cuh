@@ -125,6 +125,21 @@ __device__ __forceinline__ float rvq_butterfly(float p) {
     return p;
 }
 
+// The same sums for 32 columns at once: in place, p[0..31] (this lane's partials of 32 columns) -> p[0] = the
+// canonical sum of column `lane` (31 shuffles instead of 160; the additions and their order are those of rvq_butterfly).
+__device__ __forceinline__ void rvq_transposed_butterfly(float (&p)[32], int lane) {
+#pragma unroll
+    for (int half = 16; half >= 1; half >>= 1) {
+        const bool up = (lane & half) != 0;
+#pragma unroll
+        for (int i = 0; i < half; ++i) {
+            float send = up ? p[i] : p[i + half];
+            float keep = up ? p[i + half] : p[i];
+            p[i] = __fadd_rn(keep, __shfl_xor_sync(0xffffffffu, send, half));
+        }
+    }
+}
+
 // torch.max semantics (core_vq.py:171): NaN beats everything, first index wins ties.
 __device__ __forceinline__ bool rvq_better(float s, int i, float best, int bi) {
     bool sn = s != s, bn = best != best;

@@ -19,20 +19,6 @@
 #define RVQ_EX_WARPS 8
 #define RVQ_EX_ROWS 32
 
-// In place: p[0..31] (partials of 32 columns held by this lane) -> p[0] = full sum of column `lane`.
-__device__ __forceinline__ void rvq_transposed_butterfly(float (&p)[32], int lane) {
-#pragma unroll
-    for (int half = 16; half >= 1; half >>= 1) {
-        const bool up = (lane & half) != 0;
-#pragma unroll
-        for (int i = 0; i < half; ++i) {
-            float send = up ? p[i] : p[i + half];
-            float keep = up ? p[i + half] : p[i];
-            p[i] = __fadd_rn(keep, __shfl_xor_sync(0xffffffffu, send, half));
-        }
-    }
-}
-
 template <int DCH, int F>
 __global__ void __launch_bounds__(RVQ_EX_WARPS * 32)
 rvq_encode_exact_kernel(const float *__restrict__ x, int64_t xs_b, int64_t xs_d, int64_t xs_t, int B, int D, int T,

@@ -90,18 +90,6 @@ __device__ __forceinline__ bool mbar_test(uint32_t bar, uint32_t parity) {
         : "memory");
     return ok != 0;
 }
-// non-blocking probe (try_wait may suspend the thread for a while before it answers)
-__device__ __forceinline__ bool mbar_probe(uint32_t bar, uint32_t parity) {
-    uint32_t ok;
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-        "selp.u32 %0, 1, 0, p;\n\t}"
-        : "=r"(ok)
-        : "r"(bar), "r"(parity)
-        : "memory");
-    return ok != 0;
-}
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     while (!mbar_test(bar, parity)) {}
 }
@@ -125,16 +113,8 @@ __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 
-__device__ __forceinline__ void umma_f16(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
-        "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc)
-        : "memory");
-}
-// the same with the descriptors as (low, high) words: only the low word (start address field) changes from MMA
-// to MMA, so the caller's arithmetic stays 32-bit
+// descriptors as (low, high) words: only the low word (start address field) changes from MMA to MMA, so the
+// caller's arithmetic stays 32-bit
 __device__ __forceinline__ void umma_f16_lh(uint32_t d_tmem, uint32_t alo, uint32_t ahi, uint32_t blo, uint32_t bhi,
                                             uint32_t idesc, uint32_t acc) {
     asm volatile(
@@ -218,19 +198,6 @@ __device__ __forceinline__ uint64_t desc_interleaved(uint32_t saddr) {
 }
 
 // ------------------------------------------------------------------------------------ exact helpers
-// In place: p[0..31] (this lane's partials of 32 columns) -> p[0] = canonical sum of column `lane`.
-__device__ __forceinline__ void transposed_butterfly32(float (&p)[32], int lane) {
-#pragma unroll
-    for (int half = 16; half >= 1; half >>= 1) {
-        const bool up = (lane & half) != 0;
-#pragma unroll
-        for (int i = 0; i < half; ++i) {
-            float send = up ? p[i] : p[i + half];
-            float keep = up ? p[i + half] : p[i];
-            p[i] = __fadd_rn(keep, __shfl_xor_sync(0xffffffffu, send, half));
-        }
-    }
-}
 // 8 columns: after the three halving rounds lane l holds column (l >> 2) & 7; two plain rounds finish it.
 __device__ __forceinline__ float transposed_butterfly8(float (&p)[8], int lane) {
 #pragma unroll
@@ -299,7 +266,7 @@ __device__ __noinline__ int exact_scan_frame(float4 rf, float xx, const float *_
             a = __fmaf_rn(rf.z, e.z, a);
             p[j] = __fmaf_rn(rf.w, e.w, a);
         }
-        transposed_butterfly32(p, lane);
+        rvq_transposed_butterfly(p, lane);
         const int col = c0 + lane;
         const float s = rvq_score(xx, p[0], cnk[col]);
         if (rvq_better(s, col, best, bidx)) { best = s; bidx = col; }

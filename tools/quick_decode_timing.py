@@ -10,7 +10,7 @@ import torch
 from audiocraft_b200 import _lib
 from audiocraft_b200.quantization import ResidualVectorQuantizer
 
-B, K, T, C, D = 256, 4, 3000, 2048, 128
+B, K, T, C, D = (int(os.environ.get("DEC_B", 256)), 4, int(os.environ.get("DEC_T", 3000)), 2048, 128)
 torch.manual_seed(0)
 m = ResidualVectorQuantizer(dimension=D, n_q=K, bins=C, kmeans_init=False).cuda().eval()
 vq = m.vq
@@ -46,4 +46,4 @@ for name in (sys.argv[1:] or ["prod"]):
     ts.sort()
     us = ts[len(ts) // 2]
     nbytes = B * T * (8 * K + 4 * D)
-    print(f"[{name}] decode c4: med {us:.1f} us (min {ts[0]:.1f})  {nbytes / us / 1e3:.0f} GB/s  same output: {ok}", flush=True)
+    print(f"[{name}] decode B={B} T={T}: med {us:.1f} us (min {ts[0]:.1f})  {nbytes / us / 1e3:.0f} GB/s  same output: {ok}", flush=True)

@@ -214,17 +214,6 @@ static int launch_decode(const void *codes, const int64_t cs[3], int B, int K, i
     }
 }
 
-// Used by the encode path for the eval-forward quantized output: codes [K][B][T] int64 contiguous
-// (just written by the encode kernel) -> out [B][T][D] contiguous.
-int rvq_decode_launch_internal(const int64_t *codes_kbt, int B, int K, int T, const RvqPackView &pv, float *out,
-                               int64_t *status, cudaStream_t stream) {
-    const int64_t cs[3] = {(int64_t)T, (int64_t)B * T, 1};
-    const int64_t os[3] = {(int64_t)T * pv.D, 1, (int64_t)pv.D};
-    RvqStageOffsets koff;
-    for (int k = 0; k < RVQ_MAX_STAGES; ++k) koff.v[k] = 0;
-    return launch_decode<long long>(codes_kbt, cs, B, K, T, pv, out, os, status, koff, stream);
-}
-
 // K == 0: the reference returns the scalar 0.0; the wrapper never calls with K == 0 on a
 // non-empty output, but keep the ABI total: fill with +0.0f.
 __global__ void rvq_fill_zero_kernel(float *__restrict__ out, int64_t os_b, int64_t os_d, int64_t os_t, int B,

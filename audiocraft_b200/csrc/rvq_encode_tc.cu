@@ -19,7 +19,8 @@
 //       overflow): whole groups or the whole codebook re-scored in place.  The emitted code is the
 //       one the exact scan (rvq_encode_exact.cu) emits, bit for bit.
 //   then the residual update r -= E_k[code] through the L2-resident scratch, and the fp16 operand
-//   row of the next stage.
+//   row of the next stage.  With a quantized output requested (eval forward), the tile's frames are
+//   summed from their K winner rows in stage order after the last stage (template flag QOUT).
 //
 // A CTA runs two 128-frame tiles ("slots") in lock step: both are at the same codebook tile at the
 // same time, so one copy of the tile serves 256 frames.  Warp roles (12 warps):
@@ -378,6 +379,8 @@ struct TcParams {
     int C, K, NT;         // NT = C / 128
     int64_t *codes;       // [K][N]
     RvqWire wire;         // optional int16 copy of the codes (frame-sharded jobs)
+    float *quantized;     // optional quantized_out, element (b, t, d) at quantized[b * qs_b + t * qs_t + d]
+    int64_t qs_b, qs_t;
     float *scratch;       // residuals of the tiles in flight: [grid][2 slots][128 frames][128] fp32
     float *vals;          // approximate scores of the remembered groups: [grid][2 slots][LISTCAP][128 frames][16]
     // diagnostics (optional): accumulators and per-frame scan state of CTA 0 / slot 0 / first tile
@@ -395,7 +398,7 @@ __device__ __forceinline__ int slot_tiles(int ntiles, int grid, int cta, int slo
 }
 
 // ------------------------------------------------------------------------------------ kernel
-template <bool DBG, bool TIMING>
+template <bool DBG, bool TIMING, bool QOUT>
 __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParams P) {
     extern __shared__ uint8_t smem_raw[];
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -991,6 +994,47 @@ __global__ void __launch_bounds__(THREADS, 1) rvq_encode_tc_kernel(const TcParam
                 RVQ_TL(0x370)
                 RVQ_LAP(7)
             }
+            if (QOUT) {
+                // quantized_out = 0.0 + E_0[code_0] + E_1[code_1] + ... in stage order (core_vq.py:363-385) for this warp's
+                // 32 frames: warp = frame, lane = 4 dims; eight frames and two stages (16 rows) in flight
+                // (four stages at once spill: the compiler gives this code the registers of the scan loop, not more).  The codes are
+                // the ones this thread has just written (thread = frame), read back and passed round by shuffles.
+                const int64_t qoff = n_l < P.N ? (n_l / P.T) * P.qs_b + (n_l % P.T) * P.qs_t : -1;
+#pragma unroll 1
+                for (int f0 = 0; f0 < 32; f0 += 8) {
+                    float4 acc[8];
+#pragma unroll
+                    for (int t = 0; t < 8; ++t) acc[t] = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 1
+                    for (int k0 = 0; k0 < K; k0 += 2) {
+                        const bool two = k0 + 1 < K;
+                        const int ca = n_l < P.N ? (int)P.codes[(int64_t)k0 * P.N + n_l] : 0;
+                        const int cb = (two && n_l < P.N) ? (int)P.codes[(int64_t)(k0 + 1) * P.N + n_l] : 0;
+                        const float *Ea = P.embed + (size_t)k0 * C * 128 + lane * 4;
+                        const float *Eb = Ea + (size_t)(two ? C : 0) * 128;
+                        float4 ra[8], rb[8];
+#pragma unroll
+                        for (int t = 0; t < 8; ++t) {
+                            ra[t] = __ldg(reinterpret_cast<const float4 *>(Ea + (size_t)__shfl_sync(0xffffffffu, ca, f0 + t) * 128));
+                            rb[t] = __ldg(reinterpret_cast<const float4 *>(Eb + (size_t)__shfl_sync(0xffffffffu, cb, f0 + t) * 128));
+                        }
+#pragma unroll
+                        for (int t = 0; t < 8; ++t) {
+                            acc[t].x = __fadd_rn(acc[t].x, ra[t].x); acc[t].y = __fadd_rn(acc[t].y, ra[t].y);
+                            acc[t].z = __fadd_rn(acc[t].z, ra[t].z); acc[t].w = __fadd_rn(acc[t].w, ra[t].w);
+                            if (two) {
+                                acc[t].x = __fadd_rn(acc[t].x, rb[t].x); acc[t].y = __fadd_rn(acc[t].y, rb[t].y);
+                                acc[t].z = __fadd_rn(acc[t].z, rb[t].z); acc[t].w = __fadd_rn(acc[t].w, rb[t].w);
+                            }
+                        }
+                    }
+#pragma unroll
+                    for (int t = 0; t < 8; ++t) {
+                        const int64_t o = __shfl_sync(0xffffffffu, qoff, f0 + t);
+                        if (o >= 0) __stcs(reinterpret_cast<float4 *>(P.quantized + o) + lane, acc[t]);
+                    }
+                }
+            }
         }
     }
     if (TIMING && cta == 0 && lane == 0 && P.dbg_time) {
@@ -1039,7 +1083,7 @@ static int tc_grid(int64_t N, int sms) {
     return (int)(grid < 1 ? 1 : grid);
 }
 
-// workspace = [256 B: decode status word] [grid x 128 KB: residuals] [grid x 256 KB: remembered approximate scores]
+// workspace = [256 B: reserved] [grid x 128 KB: residuals] [grid x 256 KB: remembered approximate scores]
 constexpr int64_t WS_HEADER = 256;
 constexpr int64_t WS_R_PER_CTA = (int64_t)NSLOT * TILE_M * 128 * 4;              // residuals
 constexpr int64_t WS_V_PER_CTA = (int64_t)NSLOT * LISTCAP * TILE_M * 16 * 4;   // remembered approximate scores
@@ -1052,11 +1096,8 @@ int64_t rvq_tc_workspace_bytes(int B, int D, int T, int K, int C) {
     return WS_HEADER + WS_PER_CTA * tc_grid((int64_t)B * T, sms);
 }
 
-int rvq_decode_launch_internal(const int64_t *codes_kbt, int B, int K, int T, const RvqPackView &pv, float *out,
-                               int64_t *status, cudaStream_t stream);
-
 static int launch_tc(const float *x, const int64_t xs[3], int B, int T, const RvqPackView &pv, int K, int64_t *codes,
-                     const RvqWire &wire, void *workspace, int64_t workspace_bytes, float *dbg_acc, float *dbg_info, int dbg_stage,
+                     float *quantized, const RvqWire &wire, void *workspace, int64_t workspace_bytes, float *dbg_acc, float *dbg_info, int dbg_stage,
                      cudaStream_t stream, bool fit_grid_to_workspace = false) {
     TcParams P;
     P.x = x; P.xs_b = xs[0]; P.xs_d = xs[1]; P.xs_t = xs[2];
@@ -1067,6 +1108,7 @@ static int launch_tc(const float *x, const int64_t xs[3], int B, int T, const Rv
     P.C = pv.C; P.K = K; P.NT = pv.C / 128;
     P.codes = codes;
     P.wire = wire;
+    P.quantized = quantized; P.qs_b = (int64_t)T * 128; P.qs_t = 128;  // [B][T][D] contiguous
     P.dbg_acc = dbg_acc; P.dbg_info = dbg_info; P.dbg_stage = dbg_stage;
     P.dbg_time = dbg_info ? reinterpret_cast<long long *>(dbg_info + 128 * 8) : nullptr;  // info_out: 128*8 floats + 96 int64
     int sms = 0;
@@ -1086,14 +1128,19 @@ static int launch_tc(const float *x, const int64_t xs[3], int B, int T, const Rv
 #else
     if (dbg_acc) {
 #endif
-        RVQ_CUDA(cudaFuncSetAttribute(rvq_encode_tc_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_ALLOC));
-        rvq_encode_tc_kernel<true, true><<<grid, THREADS, SM_ALLOC, stream>>>(P);
+        RVQ_CUDA(cudaFuncSetAttribute(rvq_encode_tc_kernel<true, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_ALLOC));
+        rvq_encode_tc_kernel<true, true, false><<<grid, THREADS, SM_ALLOC, stream>>>(P);
     } else if (dbg_info) {  // cycle counters only: the production code path plus clock reads
-        RVQ_CUDA(cudaFuncSetAttribute(rvq_encode_tc_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_ALLOC));
-        rvq_encode_tc_kernel<false, true><<<grid, THREADS, SM_ALLOC, stream>>>(P);
+        RVQ_CUDA(cudaFuncSetAttribute(rvq_encode_tc_kernel<false, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_ALLOC));
+        rvq_encode_tc_kernel<false, true, false><<<grid, THREADS, SM_ALLOC, stream>>>(P);
     } else {
-        RVQ_CUDA(cudaFuncSetAttribute(rvq_encode_tc_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_ALLOC));
-        rvq_encode_tc_kernel<false, false><<<grid, THREADS, SM_ALLOC, stream>>>(P);
+        if (quantized) {
+            RVQ_CUDA(cudaFuncSetAttribute(rvq_encode_tc_kernel<false, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_ALLOC));
+            rvq_encode_tc_kernel<false, false, true><<<grid, THREADS, SM_ALLOC, stream>>>(P);
+        } else {
+            RVQ_CUDA(cudaFuncSetAttribute(rvq_encode_tc_kernel<false, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_ALLOC));
+            rvq_encode_tc_kernel<false, false, false><<<grid, THREADS, SM_ALLOC, stream>>>(P);
+        }
     }
     rvq_count_launch(1);
     return rvq_check_launch("rvq_encode_tc_kernel");
@@ -1103,12 +1150,9 @@ int rvq_encode_tc(const float *x, const int64_t xs[3], int B, int D, int T, cons
                   int K, int64_t *codes, float *quantized, const RvqWire &wire, void *workspace, int64_t workspace_bytes,
                   cudaStream_t stream, bool fit_grid_to_workspace) {
     (void)pack; (void)D;
-    int rc = launch_tc(x, xs, B, T, pv, K, codes, wire, workspace, workspace_bytes, nullptr, nullptr, 0, stream,
-                       fit_grid_to_workspace);
-    if (rc != RVQ_OK || !quantized) return rc;
-    // quantized_out = 0 + q_0 + ... (core_vq.py:363-385): the gather-sum kernel on the codes just written
-    RVQ_CUDA(cudaMemsetAsync(workspace, 0, 16, stream));
-    return rvq_decode_launch_internal(codes, B, K, T, pv, quantized, (int64_t *)workspace, stream);
+    // quantized_out = 0 + q_0 + ... (core_vq.py:363-385) is written by the same kernel, tile by tile
+    return launch_tc(x, xs, B, T, pv, K, codes, quantized, wire, workspace, workspace_bytes, nullptr, nullptr, 0, stream,
+                     fit_grid_to_workspace);
 }
 
 // Diagnostics: raw tensor-core accumulators and scan state of the first 128 frames, stage `stage`.
@@ -1119,7 +1163,7 @@ extern "C" int rvq_debug_tc_scores(const float *x, const int64_t xs[3], int B, i
     RVQ_REQUIRE(rvq_tc_shape_supported(D, C) && K > 0 && K <= Ktot && stage >= 0 && stage < K, RVQ_EUNSUPPORTED,
                 "rvq_debug_tc_scores: shape not covered by the tensor-core path");
     RvqPackView pv = rvq_pack_view(pack, Ktot, C, D);
-    return launch_tc(x, xs, B, T, pv, K, codes, RvqWire{nullptr, 0, 0}, workspace, workspace_bytes, acc_out, info_out, stage,
+    return launch_tc(x, xs, B, T, pv, K, codes, nullptr, RvqWire{nullptr, 0, 0}, workspace, workspace_bytes, acc_out, info_out, stage,
                      (cudaStream_t)stream_);
 }
 
@@ -1171,8 +1215,8 @@ extern "C" int rvq_encode_f32_static(const float *x, const int64_t xs[3], int B,
     int rc = static_scratch_address(&scratch);
     if (rc != RVQ_OK) return rc;
     RvqPackView pv = rvq_pack_view(pack, Ktot, C, D);
-    // The array still holds what the previous call left.  The residual / score areas are fully rewritten before
-    // they are read; the status word of the gather-sum kernel must start at zero and is cleared inside rvq_encode_tc.
+    // The array still holds what the previous call left: the residual / score areas are fully rewritten before
+    // they are read.
     return rvq_encode_tc(x, xs, B, D, T, pack, pv, K, codes, quantized, RvqWire{nullptr, 0, 0}, scratch,
                          (int64_t)sizeof(g_static_scratch), stream,
                          /*fit_grid_to_workspace=*/true);

@@ -5,7 +5,7 @@
 // reproduce bit for bit, the path taken for shapes / inputs the tensor-core search is not
 // certified for (D % 64 != 0, non-finite codebooks, extreme scales), and RVQ_ALGO_EXACT.
 //
-// Work split: a warp owns F frames for all K stages; lane l keeps elements 128*ch + 4*l + {0..3} of
+// Work split: a warp owns F frames for all K stages (F chosen by the host from D and the frame count); lane l keeps elements 128*ch + 4*l + {0..3} of
 // each frame's residual in registers (never written back).  A block of 8 warps streams the stage's
 // codebook through shared memory in tiles of 32 rows, so each row is fetched from L2 once per
 // 8*F frames.  Per tile every lane forms its 4*DCH-element partial of 32 inner products per frame;
@@ -171,8 +171,16 @@ int rvq_encode_exact(const float *x, const int64_t xs[3], int B, int D, int T, c
                      int64_t *codes, float *quantized, const RvqWire &wire, cudaStream_t stream) {
     RVQ_REQUIRE(D <= 512, RVQ_EUNSUPPORTED, "rvq_encode_f32: dimension %d > 512 is not implemented", D);
     RVQ_REQUIRE((int64_t)B * T <= (int64_t)INT_MAX * 8, RVQ_EUNSUPPORTED, "rvq_encode_f32: too many frames");
-    if (D <= 128) return launch_exact<1, 2>(x, xs, B, D, T, pv, K, codes, quantized, wire, stream);
-    if (D <= 256) return launch_exact<2, 1>(x, xs, B, D, T, pv, K, codes, quantized, wire, stream);
-    if (D <= 384) return launch_exact<3, 1>(x, xs, B, D, T, pv, K, codes, quantized, wire, stream);
-    return launch_exact<4, 1>(x, xs, B, D, T, pv, K, codes, quantized, wire, stream);
+    // Frames per warp: every shared-memory read of a codebook row feeds 4 F multiply-adds, so more frames per warp
+    // take the kernel off the shared-memory pipe (D = 256: 4.0 -> 2.5 ms on 24 000 frames) -- when there are enough
+    // frames to keep every SM's eight warps busy with that many each.
+    const int64_t N = (int64_t)B * T;
+    const bool many = N >= (int64_t)8 * 148 * 8 * 2, some = N >= (int64_t)4 * 148 * 8 * 2;
+#define RVQ_EX_GO(DCH, F) return launch_exact<DCH, F>(x, xs, B, D, T, pv, K, codes, quantized, wire, stream)
+    if (D <= 128) { if (many) RVQ_EX_GO(1, 8); RVQ_EX_GO(1, 2); }
+    if (D <= 256) { if (some) RVQ_EX_GO(2, 4); RVQ_EX_GO(2, 1); }
+    if (D <= 384) { if (some) RVQ_EX_GO(3, 2); RVQ_EX_GO(3, 1); }
+    if (some) RVQ_EX_GO(4, 2);
+    RVQ_EX_GO(4, 1);
+#undef RVQ_EX_GO
 }

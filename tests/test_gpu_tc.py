@@ -58,7 +58,8 @@ def test_tc_scores_are_within_the_certified_bound(stage):
     assert np.array_equal(codes, want)
 
 
-@pytest.mark.parametrize("shape", [(4, 2048, 3, 700), (32, 1024, 2, 301), (8, 2048, 1, 129), (2, 256, 5, 64)])
+@pytest.mark.parametrize("shape", [(4, 2048, 3, 700), (32, 1024, 2, 301), (8, 2048, 1, 129), (2, 256, 5, 64),
+                                   (3, 2048, 2, 333), (1, 512, 7, 100)])  # odd stage counts: the quantized sum walks stages in pairs
 def test_tc_codes_equal_oracle(shape):
     K, C, B, T = shape
     embed = gen.codebooks(100 + K, K, C, 128)

@@ -24,7 +24,7 @@ __global__ void __launch_bounds__(RVQ_EX_WARPS * 32)
 rvq_encode_exact_kernel(const float *__restrict__ x, int64_t xs_b, int64_t xs_d, int64_t xs_t, int B, int D, int T,
                         const float *__restrict__ embed, const float *__restrict__ cnorm, int C, int K,
                         int64_t *__restrict__ codes, float *__restrict__ quantized, const RvqWire wire) {
-    extern __shared__ float4 s_tile[];  // [RVQ_EX_ROWS][DCH * 32] float4
+    extern __shared__ float4 s_tile[];  // 2 x [RVQ_EX_ROWS][DCH * 32] float4
     const int lane = threadIdx.x & 31;
     const int wib = threadIdx.x >> 5;
     const int64_t N = (int64_t)B * T;
@@ -63,16 +63,32 @@ rvq_encode_exact_kernel(const float *__restrict__ x, int64_t xs_b, int64_t xs_d,
             bidx[f] = INT_MAX;
         }
 
-        for (int c0 = 0; c0 < C; c0 += RVQ_EX_ROWS) {
-            __syncthreads();  // the previous tile has been consumed by every warp
-            for (int i = threadIdx.x; i < RVQ_EX_ROWS * DCH * 32; i += RVQ_EX_WARPS * 32) {
+        // codebook tiles of 32 rows, double-buffered: the next tile travels (cp.async, zero-filled past C and D)
+        // while this one is scored
+        constexpr int TILE4 = RVQ_EX_ROWS * DCH * 32;  // float4 per tile
+        auto issue_tile = [&](int c0, int buf) {
+            for (int i = threadIdx.x; i < TILE4; i += RVQ_EX_WARPS * 32) {
                 const int row = i / (DCH * 32), c4 = i % (DCH * 32);
                 const int c = c0 + row, d = c4 * 4;
-                float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (c < C && d < D) v = __ldg(reinterpret_cast<const float4 *>(Ek + (int64_t)c * D + d));
-                s_tile[i] = v;
+                const bool ok = c < C && d < D;
+                const float *src = ok ? Ek + (int64_t)c * D + d : Ek;
+                const uint32_t dst = (uint32_t)__cvta_generic_to_shared(s_tile + buf * TILE4 + i);
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(ok ? 16 : 0) : "memory");
+            }
+            asm volatile("cp.async.commit_group;" ::: "memory");
+        };
+        __syncthreads();  // the previous stage's last tile has been consumed by every warp
+        issue_tile(0, 0);
+        for (int c0 = 0, tix = 0; c0 < C; c0 += RVQ_EX_ROWS, ++tix) {
+            const int buf = tix & 1;
+            if (c0 + RVQ_EX_ROWS < C) {
+                issue_tile(c0 + RVQ_EX_ROWS, buf ^ 1);
+                asm volatile("cp.async.wait_group 1;" ::: "memory");
+            } else {
+                asm volatile("cp.async.wait_group 0;" ::: "memory");
             }
             __syncthreads();
+            const float4 *tile = s_tile + buf * TILE4;
 
             float p[F][32];
 #pragma unroll
@@ -81,7 +97,7 @@ rvq_encode_exact_kernel(const float *__restrict__ x, int64_t xs_b, int64_t xs_d,
                 for (int f = 0; f < F; ++f) p[f][j] = 0.0f;
 #pragma unroll
                 for (int ch = 0; ch < DCH; ++ch) {
-                    const float4 e = s_tile[j * (DCH * 32) + ch * 32 + lane];
+                    const float4 e = tile[j * (DCH * 32) + ch * 32 + lane];
 #pragma unroll
                     for (int f = 0; f < F; ++f) {
                         p[f][j] = __fmaf_rn(r[f][ch][0], e.x, p[f][j]);
@@ -101,6 +117,7 @@ rvq_encode_exact_kernel(const float *__restrict__ x, int64_t xs_b, int64_t xs_d,
                     if (rvq_better(s, col, best[f], bidx[f])) { best[f] = s; bidx[f] = col; }
                 }
             }
+            __syncthreads();  // this buffer is refilled by the next iteration's prefetch
         }
 
         // arg-max across lanes, residual update, quantized accumulation
@@ -158,7 +175,7 @@ static int launch_exact(const float *x, const int64_t xs[3], int B, int D, int T
     const int64_t N = (int64_t)B * T;
     const int64_t per_block = (int64_t)RVQ_EX_WARPS * F;
     const int64_t blocks = (N + per_block - 1) / per_block;
-    const size_t smem = (size_t)RVQ_EX_ROWS * DCH * 32 * sizeof(float4);
+    const size_t smem = (size_t)2 * RVQ_EX_ROWS * DCH * 32 * sizeof(float4);
     auto kern = rvq_encode_exact_kernel<DCH, F>;
     if (smem > 48 * 1024) RVQ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     kern<<<(unsigned)blocks, RVQ_EX_WARPS * 32, smem, stream>>>(x, xs[0], xs[1], xs[2], B, D, T, pv.embed, pv.cnorm,

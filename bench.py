@@ -380,6 +380,14 @@ def run_gpu_arm(args, rank: int, world: int, local_rank: int):
 
     no_events = [_NoEvent()] * 3
 
+    # The decode of a step runs on a second stream of lower priority: the next step's encode does not depend on it, so
+    # its thread blocks fill the SMs that the encode kernel's CTAs leave as they finish (config 2's 750 tiles leave
+    # 138 of 148 CTAs done a tenth of the kernel's time before the ten that own six tiles).  BENCH_SERIAL=1: one stream.
+    overlap = not os.environ.get("BENCH_SERIAL")
+    main_stream = torch.cuda.Stream(dev, priority=-1) if overlap else torch.cuda.current_stream(dev)
+    dec_stream = torch.cuda.Stream(dev, priority=0) if overlap else None
+    enc_done = [torch.cuda.Event() for _ in range(8)]
+
     def step(i, e3=no_events):
         """One step, the same code (and so the same allocation pattern) untimed and timed: encode, decode, and for
         N > 1 the all-gather of the codes on a side stream (the next batch does not depend on the gathered codes).
@@ -388,8 +396,17 @@ def run_gpu_arm(args, rank: int, world: int, local_rank: int):
         e3[0].record()
         codes = encode_step(x)
         e3[1].record()
-        q = m.decode(codes)
-        e3[2].record()
+        if overlap:
+            ed = enc_done[i % len(enc_done)]
+            ed.record()
+            dec_stream.wait_event(ed)
+            with torch.cuda.stream(dec_stream):
+                q = m.decode(codes)
+                e3[2].record()
+            codes.record_stream(dec_stream)
+        else:
+            q = m.decode(codes)
+            e3[2].record()
         if world > 1:
             _, gathered = sharded.gather_codes_async(codes, gshape)  # int16 on the wire, widened by one kernel
             return gathered
@@ -424,7 +441,7 @@ def run_gpu_arm(args, rank: int, world: int, local_rank: int):
     gate_group = dist.new_group(backend="gloo") if world > 1 else None  # host-side agreement, no GPU work
 
     # ---- device-resident timing -------------------------------------------------------------
-    with torch.no_grad():
+    with torch.no_grad(), torch.cuda.stream(main_stream):
         # the sampling thread is started before the warm-up so that its start-up cost is not in the timed region
         sampler = ClockSampler(local_rank) if rank == 0 and not os.environ.get("BENCH_NO_SAMPLER") else None
         if sampler:
@@ -477,6 +494,8 @@ def run_gpu_arm(args, rank: int, world: int, local_rank: int):
                 gate = None
         if world > 1:
             torch.cuda.current_stream(dev).wait_event(gathered)  # every all-gather ends inside the timed region
+        if overlap:
+            torch.cuda.current_stream(dev).wait_stream(dec_stream)  # ... and every decode
         end.record()
         sync_all()
         gc.enable()
@@ -492,7 +511,24 @@ def run_gpu_arm(args, rank: int, world: int, local_rank: int):
     log("[bench] per-step host enqueue ms: " + " ".join(f"{(b - a) * 1e3:.3f}" for a, b in zip(host_t, host_t[1:])))
     log("[bench] per-step encode ms: " + " ".join(f"{e[0].elapsed_time(e[1]):.3f}" for e in ev))
     enc_ms = sum(e[0].elapsed_time(e[1]) for e in ev) / args.steps
-    dec_ms = sum(e[1].elapsed_time(e[2]) for e in ev) / args.steps
+    if overlap:
+        # the decode kernel alone (in the steps it shares the GPU with the next encode): a serial loop after the timing
+        with torch.no_grad():
+            cs2 = [m.encode(xs[i]) for i in range(2)]
+            for i in range(4):
+                q = m.decode(cs2[i % 2])
+            torch.cuda.synchronize(dev)
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            torch.cuda._sleep(6_000_000)  # ~3 ms of GPU spin: the 20 launches are queued before the first one runs
+            a.record()
+            for i in range(20):
+                q = m.decode(cs2[i % 2])
+            b.record()
+            torch.cuda.synchronize(dev)
+            dec_ms = a.elapsed_time(b) / 20
+            del cs2, q
+    else:
+        dec_ms = sum(e[1].elapsed_time(e[2]) for e in ev) / args.steps
     t = torch.tensor([elapsed_ms], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -633,6 +669,9 @@ def run_gpu_arm(args, rank: int, world: int, local_rank: int):
                    "encode_algo": m.vq.encode_algo,
                    "untimed_steps_before_timing": args.warmup + 20 + int(extra.item()),
                    "start": "timed region enqueued behind a gate kernel opened at an agreed wall-clock time",
+                   "streams": ("encode on a high-priority stream, the decode of every step on a second stream (it fills the "
+                               "SMs the encode kernel's CTAs leave as they finish); all complete inside the timed region")
+                   if overlap else "one stream",
                    "collective": ("codes of every step exchanged as int16 (" + exchange_kind + "), side stream, all complete "
                                   "inside the timed region") if world > 1 else "none"},
         "roofline": roofline,

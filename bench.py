@@ -385,14 +385,34 @@ def run_gpu_arm(args, rank: int, world: int, local_rank: int):
     # 138 of 148 CTAs done a tenth of the kernel's time before the ten that own six tiles).  BENCH_SERIAL=1: one stream.
     overlap = not os.environ.get("BENCH_SERIAL")
     main_stream = torch.cuda.Stream(dev, priority=-1) if overlap else torch.cuda.current_stream(dev)
-    dec_stream = torch.cuda.Stream(dev, priority=0) if overlap else None
+    dec_stream = torch.cuda.Stream(dev, priority=int(os.environ.get("BENCH_DEC_PRIO", "0"))) if overlap else None
     enc_done = [torch.cuda.Event() for _ in range(8)]
+    # experiment (BENCH_ENC_STREAMS=2): consecutive encodes on two streams, so that the next kernel's CTAs start on the SMs
+    # the previous kernel's CTAs have left
+    n_enc = int(os.environ.get("BENCH_ENC_STREAMS", "1")) if overlap and world == 1 else 1  # (kernel times then overlap: not the default)
+    enc_streams = [torch.cuda.Stream(dev, priority=-1) for _ in range(n_enc)] if n_enc > 1 else None
 
     def step(i, e3=no_events):
         """One step, the same code (and so the same allocation pattern) untimed and timed: encode, decode, and for
         N > 1 the all-gather of the codes on a side stream (the next batch does not depend on the gathered codes).
         Returns the event of the all-gather."""
         x = xs[i % N_ROTATING]
+        if enc_streams is not None:
+            es = enc_streams[i % n_enc]
+            es.wait_stream(torch.cuda.current_stream(dev))
+            with torch.cuda.stream(es):
+                e3[0].record()
+                codes = encode_step(x)
+                e3[1].record()
+                ed = enc_done[i % len(enc_done)]
+                ed.record()
+            codes.record_stream(es)
+            dec_stream.wait_event(ed)
+            with torch.cuda.stream(dec_stream):
+                q = m.decode(codes)
+                e3[2].record()
+            codes.record_stream(dec_stream)
+            return None
         e3[0].record()
         codes = encode_step(x)
         e3[1].record()
@@ -494,6 +514,9 @@ def run_gpu_arm(args, rank: int, world: int, local_rank: int):
                 gate = None
         if world > 1:
             torch.cuda.current_stream(dev).wait_event(gathered)  # every all-gather ends inside the timed region
+        if enc_streams is not None:
+            for es in enc_streams:
+                torch.cuda.current_stream(dev).wait_stream(es)
         if overlap:
             torch.cuda.current_stream(dev).wait_stream(dec_stream)  # ... and every decode
         end.record()
